@@ -1,0 +1,77 @@
+// Internal interfaces between the translation units of libbrp_b200.so (not part of the C ABI).
+#ifndef BRP_INTERNAL_H
+#define BRP_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/brp_b200.h"
+
+// Per-template constants as the kernels consume them (16 bytes, one float4 load).
+struct BrpTemplateDev {
+    float tau, Omega, Psi0, S0;
+};
+
+// Device-side view of the work-unit geometry.
+struct BrpGeomDev {
+    uint32_t nu;        // unpadded samples
+    uint32_t n;         // padded samples = FFT length
+    uint32_t fft_size;  // n/2 + 1
+    uint32_t w2, fu, h; // window_2, fundamental_idx_hi, harmonic_idx_hi
+    float dt, step_inv;
+};
+
+// ---------------- resampling (resamp.cu) ----------------
+static const int BRP_RESAMP_THREADS = 256;
+static const int BRP_RESAMP_SAMPLES_PER_BLOCK = 4096;
+
+inline uint32_t brp_resamp_blocks(uint32_t nu)
+{
+    return (nu + BRP_RESAMP_SAMPLES_PER_BLOCK - 1) / BRP_RESAMP_SAMPLES_PER_BLOCK;
+}
+
+// out: batch x out_stride floats; [0, n_steps) of each row is written (and [n_steps, n) with the mean when
+// fill_padding).  idx_out (batch x nu int32) optional.  partials: batch x brp_resamp_blocks(nu) doubles;
+// counters: batch uint32, must be zero on entry and are left zero on exit.
+cudaError_t brp_launch_resample(const float *series, const BrpTemplateDev *tmpl, int batch, const BrpGeomDev &g,
+                                float *out, size_t out_stride, int32_t *idx_out, uint32_t *n_steps, float *mean,
+                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st);
+cudaError_t brp_launch_sin_lut(const float *x, float *out, uint32_t n, cudaStream_t st);
+cudaError_t brp_launch_round_index(const float *f, int32_t *out, uint32_t n, cudaStream_t st);
+
+// ---------------- FFT + power spectrum (fft.cu) ----------------
+struct BrpFftPlan {
+    uint32_t n;      // real length
+    uint32_t m;      // complex length n/2
+    uint32_t m1, m2; // m = m1*m2 : pass 1 transforms length m2 (stride m1), pass 2 length m1
+    int radix3;      // 1 when m2 carries the factor 3
+    float2 *tw_pass1;   // in-tile twiddles for length m2
+    float2 *tw_pass2;   // in-tile twiddles for length m1
+    float2 *tw_untangle_a; // W_n^{k2},      k2 < m2
+    float2 *tw_untangle_b; // W_{2 m1}^{k1}, k1 < m1
+    float2 *tw_inter_hi, *tw_inter_lo; // W_m^{p}: p = hi*1024 + lo
+    int smem_pass1, smem_pass2;
+    int launches_per_batch;
+};
+
+int brp_fft_plan_create(BrpFftPlan *p, uint32_t n);
+void brp_fft_plan_destroy(BrpFftPlan *p);
+// in: batch x in_stride floats (only [0, n_steps[b]) valid; the rest is taken as mean[b]);
+// work: batch x m float2; ps: batch x ps_stride floats, bins [0, ps_count) written, ps[0] = 0.
+cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in_stride, const uint32_t *n_steps,
+                                 const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
+                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event);
+
+// ---------------- harmonic summing + per-bin toplist (hs.cu) ----------------
+struct BrpThresholds {
+    float t[5];
+};
+// keys: 5 x fu uint64, key = float_bits(power) << 32 | (0xFFFFFFFF - template index); atomicMax semantics
+cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int batch, const BrpGeomDev &g,
+                                        BrpThresholds thr, uint32_t first_template, unsigned long long *keys,
+                                        cudaStream_t st);
+// compact non-zero keys with bin >= w2 into hits (device), counter (device uint32, zeroed by caller)
+cudaError_t brp_launch_collect(const unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits,
+                               uint32_t max_hits, uint32_t *counter, cudaStream_t st);
+
+#endif

@@ -1,0 +1,512 @@
+// Kernel 2: two-pass shared-memory-staged R2C FFT with fused power-spectrum epilogue (north_star kernel 2).
+//
+// Contract (what the reference gets from fftwf_plan_dft_r2c_1d + the loop in demod_binary_fft_fftw.c:88-113):
+//     P[k] = norm * |sum_{n<N} x[n] exp(-2 pi i k n / N)|^2   for 1 <= k < count,   P[0] = 0
+// where x is the resampled series mean-padded to N samples (demod_binary_resamp_cpu.c:130-133).
+// No cuFFT: the transform is written here.
+//
+// The N reals are viewed as M = N/2 complex points z[m] = x[2m] + i x[2m+1] and M = M1*M2 is split
+// four-step style, so the data makes exactly two trips through HBM:
+//
+//   pass 1 (fft_pass1_kernel): one tile = ROWS consecutive columns m1 of the M2 x M1 view; for each column
+//       a length-M2 transform over m2 (input stride M1), the padding rule applied on load
+//       (i >= n_steps -> mean, so the pad is never materialised), times the twiddle W_M^{m1*k2}, written
+//       transposed as Y[k2][m1].
+//   pass 2 (fft_pass2_kernel): one tile = T2 rows k2 and their T2 mirror rows M2-k2 of Y; a length-M1
+//       transform along each (contiguous) row gives Z[k2 + M2*k1]; row k2 and row M2-k2 hold exactly
+//       the pairs (Z[k], Z[M-k]) the real-input "untangle" needs, so the epilogue forms
+//       X[k] = E + W_N^k O, X[M-k] = conj(E - W_N^k O) and stores norm*|X|^2 for bins < count only.
+//
+// In a tile every thread keeps a radix-16 (or 8/4/2/3) butterfly in registers; stages exchange data
+// through shared memory (decimation in frequency, in place, digit-reversed result), the first stage
+// reads straight from global memory and pass 1's last stage writes straight back, so a tile crosses
+// shared memory once per stage boundary only.  Shared-memory positions are padded (+1 per 16 and per
+// 256 elements) so the power-of-two strides of the butterflies and the digit-reversed reads of the
+// epilogue stay free of bank conflicts.
+//
+// HBM traffic per template: 4N (x) + 8M (Y out) + 8M (Y in) + 4*count (P) = 12N + 4*count bytes,
+// against the algorithmic 4N + 4F of SURVEY.md 8(d).
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <vector>
+
+#include "brp_internal.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// ------------------------------------------------------------------ compile-time plan of one tile transform
+__host__ __device__ constexpr int cfg_radix(int L, int s)
+{
+    int rem = L;
+    if (rem % 3 == 0) {
+        if (s == 0) return 3;
+        rem /= 3;
+        --s;
+    }
+    while (rem > 1) {
+        const int r = rem >= 16 ? 16 : rem;
+        if (s == 0) return r;
+        rem /= r;
+        --s;
+    }
+    return 0;
+}
+__host__ __device__ constexpr int cfg_stages(int L)
+{
+    int s = 0;
+    while (cfg_radix(L, s) != 0) ++s;
+    return s;
+}
+// sub-transform length entering stage s
+__host__ __device__ constexpr int cfg_n(int L, int s)
+{
+    int n = L;
+    for (int i = 0; i < s; ++i) n /= cfg_radix(L, i);
+    return n;
+}
+__host__ __device__ constexpr int cfg_stride(int L, int s) { return cfg_n(L, s) / cfg_radix(L, s); }
+// offset of stage s in the tile twiddle table: stage s holds (R-1)*S entries, index (q-1)*S + p
+__host__ __device__ constexpr int cfg_tw_offset(int L, int s)
+{
+    int off = 0;
+    for (int i = 0; i < s; ++i) off += (cfg_radix(L, i) - 1) * cfg_stride(L, i);
+    return off;
+}
+__host__ __device__ constexpr int cfg_tw_size(int L) { return cfg_tw_offset(L, cfg_stages(L)); }
+
+__host__ __device__ constexpr int phys(int pos) { return pos + (pos >> 4) + (pos >> 8); }
+// row pitch: phys(L) rounded up so that (pitch mod 16) spreads ROWS rows over the 16 eight-byte banks
+__host__ __device__ constexpr int cfg_pitch(int L, int rows)
+{
+    const int want = rows >= 16 ? 1 : 16 / rows;
+    const int base = phys(L);
+    return base + ((want - base % 16) + 16) % 16;
+}
+__host__ __device__ constexpr int cfg_rows(int L)
+{
+    const int tile = (L % 3 == 0) ? 12288 : 8192;
+    return tile / L < 2 ? 2 : tile / L;
+}
+
+// ------------------------------------------------------------------ complex helpers
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cmul(float2 a, float2 b)
+{
+    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+
+// multiply by exp(-2 pi i e / 16), e = 0..7
+template <int E>
+__device__ __forceinline__ float2 mul_w16(float2 d)
+{
+    constexpr float C1 = 0.92387953251128673848f, S1 = 0.38268343236508978178f, H = 0.70710678118654752440f;
+    if constexpr (E == 0) return d;
+    else if constexpr (E == 1) return make_float2(fmaf(d.x, C1, d.y * S1), fmaf(d.y, C1, -d.x * S1));
+    else if constexpr (E == 2) return make_float2((d.x + d.y) * H, (d.y - d.x) * H);
+    else if constexpr (E == 3) return make_float2(fmaf(d.x, S1, d.y * C1), fmaf(d.y, S1, -d.x * C1));
+    else if constexpr (E == 4) return make_float2(d.y, -d.x);
+    else if constexpr (E == 5) return make_float2(fmaf(d.y, C1, -d.x * S1), -fmaf(d.x, C1, d.y * S1));
+    else if constexpr (E == 6) return make_float2((d.y - d.x) * H, -(d.x + d.y) * H);
+    else return make_float2(fmaf(d.y, S1, -d.x * C1), -fmaf(d.x, S1, d.y * C1));
+}
+
+// in-register DFT of R = 2^a points, decimation in frequency; output q ends up in v[bitrev(q)]
+template <int R>
+struct Dft {
+    template <int J>
+    static __device__ __forceinline__ void level(float2 *v)
+    {
+        if constexpr (J < R / 2) {
+            const float2 a = v[J], b = v[J + R / 2];
+            v[J] = cadd(a, b);
+            v[J + R / 2] = mul_w16<J *(16 / R)>(csub(a, b));
+            level<J + 1>(v);
+        }
+    }
+    static __device__ __forceinline__ void run(float2 *v)
+    {
+        level<0>(v);
+        Dft<R / 2>::run(v);
+        Dft<R / 2>::run(v + R / 2);
+    }
+};
+template <>
+struct Dft<1> {
+    static __device__ __forceinline__ void run(float2 *) {}
+};
+// 3-point DFT, natural output order
+template <>
+struct Dft<3> {
+    static __device__ __forceinline__ void run(float2 *v)
+    {
+        constexpr float S3 = 0.86602540378443864676f;
+        const float2 s = cadd(v[1], v[2]), d = csub(v[1], v[2]);
+        const float2 m = make_float2(fmaf(-0.5f, s.x, v[0].x), fmaf(-0.5f, s.y, v[0].y));
+        const float2 r = make_float2(S3 * d.y, -S3 * d.x); // -i * S3 * d
+        v[0] = cadd(v[0], s);
+        v[1] = cadd(m, r);
+        v[2] = csub(m, r);
+    }
+};
+
+template <int R>
+__host__ __device__ constexpr int out_slot(int q)
+{
+    if (R == 3) return q;
+    int r = 0;
+    for (int b = 1, t = R >> 1; b < R; b <<= 1, t >>= 1)
+        if (q & b) r |= t;
+    return r;
+}
+
+// frequency index of the value that ends at in-place position pos: pos = sum q_s S_s  ->  k = sum q_s (L / n_s)
+template <int L>
+__device__ __forceinline__ int freq_of_pos(int pos)
+{
+    int k = 0;
+#pragma unroll
+    for (int s = 0; s < cfg_stages(L); ++s) {
+        const int q = (pos / cfg_stride(L, s)) % cfg_radix(L, s);
+        k += q * (L / cfg_n(L, s));
+    }
+    return k;
+}
+template <int L>
+__device__ __forceinline__ int pos_of_freq(int k)
+{
+    int pos = 0;
+#pragma unroll
+    for (int s = 0; s < cfg_stages(L); ++s) {
+        const int q = (k / (L / cfg_n(L, s))) % cfg_radix(L, s);
+        pos += q * cfg_stride(L, s);
+    }
+    return pos;
+}
+
+enum { MAP_ROW_FAST = 0, MAP_BF_FAST = 1 };
+
+// One DIF stage over the whole tile.  Load(row, pos) supplies the R inputs of a butterfly, Store(row, pos, value)
+// consumes its outputs (already multiplied by the stage twiddle W_n^{p q}).
+template <int L, int ROWS, int STAGE, int MAP, typename Load, typename Store>
+__device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, Load load, Store store)
+{
+    constexpr int R = cfg_radix(L, STAGE);
+    constexpr int n = cfg_n(L, STAGE);
+    constexpr int S = cfg_stride(L, STAGE);
+    constexpr int BF = L / R; // butterflies per row
+    constexpr int ITEMS = ROWS * BF;
+    constexpr bool LAST = (STAGE == cfg_stages(L) - 1);
+    constexpr int TWO = cfg_tw_offset(L, STAGE);
+#pragma unroll 1
+    for (int item = threadIdx.x; item < ITEMS; item += kThreads) {
+        int row, bf;
+        if (MAP == MAP_ROW_FAST) {
+            row = item % ROWS;
+            bf = item / ROWS;
+        } else {
+            row = item / BF;
+            bf = item % BF;
+        }
+        const int blk = bf / S, p = bf % S;
+        const int base = blk * n + p;
+        float2 v[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) v[j] = load(row, base + j * S);
+        Dft<R>::run(v);
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            float2 o = v[out_slot<R>(q)];
+            if (!LAST && q > 0) o = cmul(o, __ldg(&tw[TWO + (q - 1) * S + p]));
+            store(row, base + q * S, o);
+        }
+    }
+}
+
+template <int L, int ROWS>
+struct SmemIO {
+    float2 *sm;
+    static constexpr int PITCH = cfg_pitch(L, ROWS);
+    __device__ __forceinline__ float2 operator()(int row, int pos) const { return sm[row * PITCH + phys(pos)]; }
+    __device__ __forceinline__ void operator()(int row, int pos, float2 v) const { sm[row * PITCH + phys(pos)] = v; }
+};
+
+// middle stages (shared -> shared), recursively unrolled over the stage index
+template <int L, int ROWS, int STAGE, int END>
+__device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm)
+{
+    if constexpr (STAGE < END) {
+        SmemIO<L, ROWS> io{sm};
+        tile_stage<L, ROWS, STAGE, MAP_BF_FAST>(tw, io, io);
+        __syncthreads();
+        tile_middle<L, ROWS, STAGE + 1, END>(tw, sm);
+    }
+}
+
+// ------------------------------------------------------------------ pass 1
+template <int L, int ROWS>
+__global__ void __launch_bounds__(kThreads)
+fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t *__restrict__ n_steps_arr,
+                 const float *__restrict__ mean_arr, float2 *__restrict__ work, uint32_t m1, uint32_t m,
+                 const float2 *__restrict__ tw)
+{
+    extern __shared__ float2 sm[];
+    constexpr int NS = cfg_stages(L);
+    const int b = blockIdx.y;
+    const uint32_t col0 = blockIdx.x * ROWS;
+    const float *x = in + (size_t)b * in_stride;
+    const uint32_t n_steps = n_steps_arr[b];
+    const float mean = mean_arr[b];
+    float2 *y = work + (size_t)b * m;
+    SmemIO<L, ROWS> io{sm};
+
+    auto gload = [&](int row, int pos) -> float2 {
+        const uint32_t col = col0 + row;
+        if (col >= m1) return make_float2(0.f, 0.f);
+        const uint32_t i = 2u * ((uint32_t)pos * m1 + col);
+        if (i + 1 < n_steps) return *reinterpret_cast<const float2 *>(x + i);
+        // mean padding on load (demod_binary_resamp_cpu.c:130-133): samples >= n_steps take the series mean
+        return make_float2(i < n_steps ? x[i] : mean, mean);
+    };
+    const float inv_m = 1.0f / (float)m;
+    auto gstore = [&](int row, int pos, float2 v) {
+        const uint32_t col = col0 + row;
+        if (col >= m1) return;
+        const uint32_t k2 = (uint32_t)freq_of_pos<L>(pos);
+        // inter-pass twiddle W_M^{col*k2}; col*k2 < M so the angle -2*pi*(col*k2)/M is reduced exactly
+        float sn, cs;
+        sincospif(-2.0f * (float)(col * k2) * inv_m, &sn, &cs);
+        y[(size_t)k2 * m1 + col] = cmul(v, make_float2(cs, sn));
+    };
+
+    if constexpr (NS == 1) {
+        tile_stage<L, ROWS, 0, MAP_ROW_FAST>(tw, gload, gstore);
+    } else {
+        tile_stage<L, ROWS, 0, MAP_ROW_FAST>(tw, gload, io);
+        __syncthreads();
+        tile_middle<L, ROWS, 1, NS - 1>(tw, sm);
+        tile_stage<L, ROWS, NS - 1, MAP_ROW_FAST>(tw, io, gstore);
+    }
+}
+
+// ------------------------------------------------------------------ pass 2 + untangle + power
+template <int L, int ROWS>
+__global__ void __launch_bounds__(kThreads)
+fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
+                 uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
+                 const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
+{
+    extern __shared__ float2 sm[];
+    constexpr int NS = cfg_stages(L);
+    constexpr int T2 = ROWS / 2;
+    constexpr uint32_t M1 = L;
+    const int b = blockIdx.y;
+    const uint32_t a = blockIdx.x * T2;
+    const float2 *y = work + (size_t)b * m;
+    float *P = ps + (size_t)b * ps_stride;
+    SmemIO<L, ROWS> io{sm};
+
+    // tile rows: r < T2 -> k2 = a + r ; r >= T2 -> k2 = (m2 - (a + r - T2)) mod m2 (the mirror row).
+    // Only rows k2 <= m2/2 (and their mirrors) are owned by a block; the grid covers k2 = 0..m2/2.
+    auto row_k2 = [&](int row) -> uint32_t {
+        const uint32_t f = a + (uint32_t)(row < T2 ? row : row - T2);
+        return row < T2 ? f : (m2 - f) % m2;
+    };
+    auto row_needed = [&](int row) -> bool {
+        const uint32_t f = a + (uint32_t)(row < T2 ? row : row - T2);
+        return 2 * f <= m2;
+    };
+    auto gload = [&](int row, int pos) -> float2 {
+        if (!row_needed(row)) return make_float2(0.f, 0.f);
+        return y[(size_t)row_k2(row) * M1 + pos];
+    };
+
+    tile_stage<L, ROWS, 0, MAP_BF_FAST>(tw, gload, io);
+    __syncthreads();
+    tile_middle<L, ROWS, 1, NS>(tw, sm);
+
+    // ---- untangle + power.  Pair (k, M-k): Z[k] in row r at k1, Z[M-k] in row r+T2 at k1' = M1-1-k1
+    // (k1' = (M1-k1) mod M1 on the self-mirrored row k2 = 0).
+    //   E = (Z[k] + conj Z[M-k])/2,  O = (Z[k] - conj Z[M-k])/(2i)
+    //   X[k] = E + W_N^k O,  X[M-k] = conj(E - W_N^k O)            (N = 2M)
+    for (int item = threadIdx.x; item < T2 * (int)M1; item += kThreads) {
+        const int r = item % T2;
+        const uint32_t k1 = item / T2;
+        const uint32_t k2 = a + r;
+        if (2 * k2 > m2) continue;
+        uint32_t k1m;
+        if (k2 == 0) {
+            if (k1 > M1 / 2) continue; // pairs (k1, M1-k1) once
+            k1m = (M1 - k1) % M1;
+        } else {
+            if (2 * k2 == m2 && k1 >= M1 / 2) continue; // row m2/2 mirrors onto itself
+            k1m = M1 - 1 - k1;
+        }
+        const float2 za = io(r, pos_of_freq<L>((int)k1));
+        const float2 zb = io(r + T2, pos_of_freq<L>((int)k1m));
+        const float2 e = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
+        const float2 d = make_float2(0.5f * (za.x - zb.x), 0.5f * (za.y + zb.y));
+        const float2 o = make_float2(d.y, -d.x);
+        const float2 w = cmul(__ldg(&tw_a[k2]), __ldg(&tw_b[k1]));
+        const float2 wo = cmul(w, o);
+        const uint32_t k = k2 + m2 * k1;
+        const uint32_t km = m - k;
+        const float2 xp = cadd(e, wo), xm = csub(e, wo);
+        if (k < ps_count) P[k] = (k == 0) ? 0.0f : norm * fmaf(xp.x, xp.x, xp.y * xp.y);
+        if (km < ps_count && km != k) P[km] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef void (*pass1_fn)(const float *, size_t, const uint32_t *, const float *, float2 *, uint32_t, uint32_t, const float2 *);
+typedef void (*pass2_fn)(const float2 *, float *, size_t, uint32_t, uint32_t, uint32_t, float, const float2 *, const float2 *,
+                         const float2 *);
+
+struct TileInfo {
+    int L, rows, smem, tw_size;
+    pass1_fn p1;
+    pass2_fn p2;
+};
+
+template <int L>
+TileInfo make_info()
+{
+    constexpr int ROWS = cfg_rows(L);
+    TileInfo t;
+    t.L = L;
+    t.rows = ROWS;
+    t.smem = ROWS * cfg_pitch(L, ROWS) * (int)sizeof(float2);
+    t.tw_size = cfg_tw_size(L);
+    t.p1 = fft_pass1_kernel<L, ROWS>;
+    t.p2 = fft_pass2_kernel<L, ROWS>;
+    return t;
+}
+
+const TileInfo *find_tile(uint32_t L)
+{
+    static const TileInfo tiles[] = {
+        make_info<16>(),   make_info<32>(),   make_info<64>(),   make_info<128>(),  make_info<256>(),
+        make_info<512>(),  make_info<1024>(), make_info<2048>(), make_info<4096>(), make_info<48>(),
+        make_info<96>(),   make_info<192>(),  make_info<384>(),  make_info<768>(),  make_info<1536>(),
+        make_info<3072>(), make_info<6144>(),
+    };
+    for (const TileInfo &t : tiles)
+        if ((uint32_t)t.L == L) return &t;
+    return nullptr;
+}
+
+// host generator for the in-tile twiddles of length L (double precision, rounded once)
+template <int L>
+void gen_tile_tw(std::vector<float2> &out)
+{
+    out.resize(cfg_tw_size(L) > 0 ? cfg_tw_size(L) : 1);
+    for (int s = 0; s + 1 < cfg_stages(L); ++s) {
+        const int R = cfg_radix(L, s), n = cfg_n(L, s), S = cfg_stride(L, s), off = cfg_tw_offset(L, s);
+        for (int q = 1; q < R; ++q)
+            for (int p = 0; p < S; ++p) {
+                const double ang = -2.0 * M_PI * (double)((long long)p * q % n) / (double)n;
+                out[off + (q - 1) * S + p] = make_float2((float)cos(ang), (float)sin(ang));
+            }
+    }
+}
+
+void gen_tile_tw_dispatch(uint32_t L, std::vector<float2> &out)
+{
+    switch (L) {
+#define C(X) case X: gen_tile_tw<X>(out); break;
+        C(16) C(32) C(64) C(128) C(256) C(512) C(1024) C(2048) C(4096)
+        C(48) C(96) C(192) C(384) C(768) C(1536) C(3072) C(6144)
+#undef C
+        default: out.clear();
+    }
+}
+
+float2 *upload(const std::vector<float2> &v)
+{
+    float2 *d = nullptr;
+    if (cudaMalloc(&d, sizeof(float2) * v.size()) != cudaSuccess) return nullptr;
+    if (cudaMemcpy(d, v.data(), sizeof(float2) * v.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaFree(d);
+        return nullptr;
+    }
+    return d;
+}
+
+} // namespace
+
+int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
+{
+    memset(p, 0, sizeof(*p));
+    if (n < 512 || (n & 1)) return RADPUL_CUDA_FFT_PLAN;
+    uint32_t m = n / 2, odd = m;
+    int a = 0;
+    while ((odd & 1) == 0) { odd >>= 1; ++a; }
+    if (odd != 1 && odd != 3) return RADPUL_CUDA_FFT_PLAN; // lengths 2^a and 3*2^a only (like the OpenCL backend)
+    // pass 2 length m1 = 2^floor(a/2); pass 1 length m2 = m / m1 carries the factor 3 if there is one
+    const uint32_t m1 = 1u << (a / 2), m2 = m / m1;
+    const TileInfo *t1 = find_tile(m2), *t2 = find_tile(m1);
+    if (!t1 || !t2) return RADPUL_CUDA_FFT_PLAN;
+    p->n = n; p->m = m; p->m1 = m1; p->m2 = m2; p->radix3 = (odd == 3);
+    p->smem_pass1 = t1->smem; p->smem_pass2 = t2->smem;
+    p->launches_per_batch = 2;
+
+    std::vector<float2> tw;
+    gen_tile_tw_dispatch(m2, tw);
+    p->tw_pass1 = upload(tw);
+    gen_tile_tw_dispatch(m1, tw);
+    p->tw_pass2 = upload(tw);
+    tw.resize(m2);
+    for (uint32_t k = 0; k < m2; ++k) {
+        const double ang = -2.0 * M_PI * (double)k / (double)n;
+        tw[k] = make_float2((float)cos(ang), (float)sin(ang));
+    }
+    p->tw_untangle_a = upload(tw);
+    tw.resize(m1);
+    for (uint32_t k = 0; k < m1; ++k) {
+        const double ang = -2.0 * M_PI * (double)k / (2.0 * (double)m1);
+        tw[k] = make_float2((float)cos(ang), (float)sin(ang));
+    }
+    p->tw_untangle_b = upload(tw);
+    if (!p->tw_pass1 || !p->tw_pass2 || !p->tw_untangle_a || !p->tw_untangle_b) {
+        brp_fft_plan_destroy(p);
+        return RADPUL_CUDA_MEM_ALLOC_DEVICE;
+    }
+    if (cudaFuncSetAttribute((const void *)t1->p1, cudaFuncAttributeMaxDynamicSharedMemorySize, t1->smem) != cudaSuccess ||
+        cudaFuncSetAttribute((const void *)t2->p2, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem) != cudaSuccess) {
+        brp_fft_plan_destroy(p);
+        return RADPUL_CUDA_FFT_PLAN;
+    }
+    return 0;
+}
+
+void brp_fft_plan_destroy(BrpFftPlan *p)
+{
+    cudaFree(p->tw_pass1);
+    cudaFree(p->tw_pass2);
+    cudaFree(p->tw_untangle_a);
+    cudaFree(p->tw_untangle_b);
+    cudaFree(p->tw_inter_hi);
+    cudaFree(p->tw_inter_lo);
+    memset(p, 0, sizeof(*p));
+}
+
+cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in_stride, const uint32_t *n_steps,
+                                 const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
+                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event)
+{
+    const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
+    const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
+    t1->p1<<<g1, kThreads, t1->smem, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (mid_event) cudaEventRecord(mid_event, st);
+    const int T2 = t2->rows / 2;
+    const dim3 g2((p.m2 / 2 + 1 + T2 - 1) / T2, batch); // rows k2 = 0 .. m2/2
+    t2->p2<<<g2, kThreads, t2->smem, st>>>(work, ps, ps_stride, ps_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
+                                           p.tw_untangle_b);
+    return cudaGetLastError();
+}

@@ -1,0 +1,276 @@
+// The reference's backend interface, one template per call, on top of the same kernels.
+//
+// These are the eleven symbols demod_binary.c calls when built with -DUSE_CUDA
+// (cuda/app/demod_binary_cuda.h:42-52, cuda/app/demod_binary_hs_cuda.cuh:37-39); state is module-global
+// exactly like in every reference backend (cuda/app/demod_binary_cuda.cu:37-59), i.e. one work-unit per
+// process, single caller thread, set_up_* once in the order resampling -> fft -> harmonic summing, run_*
+// once per template in that order.  This path exists to be a drop-in and a parity proof; throughput
+// numbers come from the batched brp_search_* layer.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "brp_internal.h"
+
+namespace {
+
+struct LegacyState {
+    bool initialised;
+    int device;
+    cudaStream_t stream;
+    // resampling
+    BrpGeomDev gd;
+    float *d_series, *d_resamp;
+    BrpTemplateDev *d_tmpl;
+    uint32_t *d_nsteps;
+    float *d_mean;
+    double *d_partials;
+    uint32_t *d_counters;
+    // fft
+    BrpFftPlan plan;
+    bool have_plan;
+    float2 *d_work;
+    float *d_ps;
+    uint32_t *d_nsteps_full;
+    float *d_mean_zero;
+    // harmonic summing
+    unsigned long long *d_keys;
+    brp_hit *d_hits, *h_hits;
+    uint32_t *d_hit_counter;
+    uint32_t hit_cap;
+    float *h_spectrum; // host copy handed out as sumspec[0]
+    uint32_t fu;
+};
+
+LegacyState L;
+
+#define LG_TRY(call, code)                                                                          \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            fprintf(stderr, "[brp_b200] %s failed: %s (%s:%d)\n", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return (code);                                                                          \
+        }                                                                                           \
+    } while (0)
+
+inline float *as_dev(DIfloatPtr p) { return reinterpret_cast<float *>(p.device_ptr); }
+
+} // namespace
+
+extern "C" {
+
+int initialize_cuda(int cudDeviceIdGiven, int *cudDeviceId)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) {
+        fprintf(stderr, "[brp_b200] no CUDA device available: this backend has no CPU fallback\n");
+        return RADPUL_CUDA_DEVICE_FIND;
+    }
+    int dev = 0;
+    if (cudDeviceIdGiven && cudDeviceId) dev = *cudDeviceId;
+    if (dev < 0 || dev >= count) return RADPUL_CUDA_DEVICE_FIND;
+    LG_TRY(cudaSetDevice(dev), RADPUL_CUDA_DEVICE_SET);
+    memset(&L, 0, sizeof(L));
+    L.device = dev;
+    LG_TRY(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking), RADPUL_CUDA_DEVICE_SET);
+    L.initialised = true;
+    if (cudDeviceId) *cudDeviceId = dev;
+    return 0;
+}
+
+int shutdown_cuda(void)
+{
+    if (!L.initialised) return 0;
+    cudaSetDevice(L.device);
+    cudaStreamSynchronize(L.stream);
+    cudaStreamDestroy(L.stream);
+    memset(&L, 0, sizeof(L));
+    return 0;
+}
+
+int set_up_resampling(DIfloatPtr input, DIfloatPtr *output, const RESAMP_PARAMS *params, float *sinLUTsamples,
+                      float *cosLUTsamples)
+{
+    (void)sinLUTsamples; // the tables of erp_utilities.cpp:45-46 are compiled into the library
+    (void)cosLUTsamples;
+    if (!L.initialised) {
+        int rc = initialize_cuda(0, NULL);
+        if (rc) return rc;
+    }
+    if (!input.host_ptr || !output || !params || params->nsamples_unpadded < 2 || params->nsamples < params->nsamples_unpadded)
+        return RADPUL_EVAL;
+    LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
+    const uint32_t nu = params->nsamples_unpadded, n = params->nsamples;
+    L.gd.nu = nu;
+    L.gd.n = n;
+    L.gd.fft_size = params->fft_size;
+    const size_t nu4 = ((size_t)nu + 3) & ~(size_t)3, n4 = ((size_t)n + 3) & ~(size_t)3;
+    LG_TRY(cudaMalloc((void **)&L.d_series, sizeof(float) * nu4), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_resamp, sizeof(float) * n4), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_tmpl, sizeof(BrpTemplateDev)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_nsteps, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_mean, sizeof(float)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_partials, sizeof(double) * brp_resamp_blocks(nu)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_counters, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMemset(L.d_counters, 0, sizeof(uint32_t)), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    // the only bulk host->device transfer of a work-unit (cuda/app/demod_binary_cuda.cu:333)
+    LG_TRY(cudaMemcpy(L.d_series, input.host_ptr, sizeof(float) * nu, cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    output->device_ptr = (brp_device_ptr_t) reinterpret_cast<uintptr_t>(L.d_resamp);
+    return 0;
+}
+
+int run_resampling(DIfloatPtr input, DIfloatPtr output, const RESAMP_PARAMS *params)
+{
+    (void)input; // the series was uploaded by set_up_resampling
+    if (!L.initialised || !L.d_series || !params || as_dev(output) != L.d_resamp) return RADPUL_EVAL;
+    LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
+    BrpGeomDev g = L.gd;
+    g.dt = params->dt;
+    g.step_inv = params->step_inv;
+    const BrpTemplateDev t = {params->tau, params->Omega, params->Psi0, params->S0};
+    LG_TRY(cudaMemcpyAsync(L.d_tmpl, &t, sizeof(t), cudaMemcpyHostToDevice, L.stream), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    const size_t n4 = ((size_t)g.n + 3) & ~(size_t)3;
+    LG_TRY(brp_launch_resample(L.d_series, L.d_tmpl, 1, g, L.d_resamp, n4, NULL, L.d_nsteps, L.d_mean, L.d_partials, L.d_counters,
+                               true, L.stream),
+           RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    return 0;
+}
+
+int tear_down_resampling(DIfloatPtr output)
+{
+    (void)output;
+    if (!L.initialised) return 0;
+    cudaSetDevice(L.device);
+    cudaFree(L.d_series); cudaFree(L.d_resamp); cudaFree(L.d_tmpl); cudaFree(L.d_nsteps); cudaFree(L.d_mean);
+    cudaFree(L.d_partials); cudaFree(L.d_counters);
+    L.d_series = L.d_resamp = NULL; L.d_tmpl = NULL; L.d_nsteps = NULL; L.d_mean = NULL; L.d_partials = NULL; L.d_counters = NULL;
+    return 0;
+}
+
+int set_up_fft(DIfloatPtr input, DIfloatPtr *output, uint32_t nsamples, unsigned int fft_size)
+{
+    (void)input;
+    if (!L.initialised || !output) return RADPUL_EVAL;
+    if (fft_size != nsamples / 2 + 1) return RADPUL_EVAL;
+    LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
+    int rc = brp_fft_plan_create(&L.plan, nsamples);
+    if (rc) {
+        fprintf(stderr, "[brp_b200] FFT length %u unsupported (2^a or 3*2^a, >= 512 / 1536)\n", nsamples);
+        return rc;
+    }
+    L.have_plan = true;
+    LG_TRY(cudaMalloc((void **)&L.d_work, sizeof(float2) * (size_t)L.plan.m), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_ps, sizeof(float) * ((size_t)fft_size + 32)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_nsteps_full, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_mean_zero, sizeof(float)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    const float zero = 0.0f;
+    LG_TRY(cudaMemcpy(L.d_nsteps_full, &nsamples, sizeof(uint32_t), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    LG_TRY(cudaMemcpy(L.d_mean_zero, &zero, sizeof(float), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    LG_TRY(cudaMemset(L.d_ps, 0, sizeof(float) * ((size_t)fft_size + 32)), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    output->device_ptr = (brp_device_ptr_t) reinterpret_cast<uintptr_t>(L.d_ps);
+    return 0;
+}
+
+int run_fft(DIfloatPtr input, DIfloatPtr output, uint32_t nsamples, unsigned int fft_size, float norm_factor)
+{
+    if (!L.initialised || !L.have_plan || nsamples != L.plan.n || as_dev(output) != L.d_ps || !as_dev(input)) return RADPUL_EVAL;
+    LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
+    // the legacy caller hands over a fully padded series, so every sample is taken from memory
+    const size_t n4 = ((size_t)nsamples + 3) & ~(size_t)3;
+    LG_TRY(brp_launch_fft_power(L.plan, as_dev(input), n4, L.d_nsteps_full, L.d_mean_zero, L.d_work, L.d_ps, (size_t)fft_size + 32,
+                                fft_size, norm_factor, 1, L.stream, NULL),
+           RADPUL_CUDA_FFT_EXEC);
+    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_FFT_EXEC);
+    return 0;
+}
+
+int tear_down_fft(DIfloatPtr output)
+{
+    (void)output;
+    if (!L.initialised) return 0;
+    cudaSetDevice(L.device);
+    if (L.have_plan) brp_fft_plan_destroy(&L.plan);
+    L.have_plan = false;
+    cudaFree(L.d_work); cudaFree(L.d_ps); cudaFree(L.d_nsteps_full); cudaFree(L.d_mean_zero);
+    L.d_work = NULL; L.d_ps = NULL; L.d_nsteps_full = NULL; L.d_mean_zero = NULL;
+    return 0;
+}
+
+int set_up_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int *nr_pages_ptr, unsigned int fundamental_idx_hi,
+                            unsigned int harmonic_idx_hi)
+{
+    (void)harmonic_idx_hi;
+    if (!L.initialised || !sumspec || !dirty || !nr_pages_ptr) return RADPUL_EVAL;
+    LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
+    const unsigned int nr_pages = (fundamental_idx_hi >> BRP_LOG_PS_PAGE_SIZE) + 1; // demod_binary_hs_cpu.c:37
+    *nr_pages_ptr = nr_pages;
+    for (int i = 1; i < 5; i++) {
+        sumspec[i] = (float *)calloc(fundamental_idx_hi ? fundamental_idx_hi : 1, sizeof(float));
+        if (!sumspec[i]) return RADPUL_EMEM;
+    }
+    for (int i = 0; i < 5; i++) {
+        dirty[i] = (int32_t *)calloc(nr_pages, sizeof(int32_t));
+        if (!dirty[i]) return RADPUL_EMEM;
+    }
+    L.fu = fundamental_idx_hi;
+    L.hit_cap = 5u * (fundamental_idx_hi ? fundamental_idx_hi : 1u);
+    LG_TRY(cudaMalloc((void **)&L.d_keys, sizeof(unsigned long long) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_hits, sizeof(brp_hit) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMalloc((void **)&L.d_hit_counter, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMallocHost((void **)&L.h_hits, sizeof(brp_hit) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_HOST);
+    LG_TRY(cudaMallocHost((void **)&L.h_spectrum, sizeof(float) * (fundamental_idx_hi ? fundamental_idx_hi : 1)), RADPUL_CUDA_MEM_ALLOC_HOST);
+    return 0;
+}
+
+int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages, DIfloatPtr powerspectrum,
+                         unsigned int window_2, unsigned int fundamental_idx_hi, unsigned int harmonic_idx_hi,
+                         float *thresholds)
+{
+    if (!L.initialised || !L.d_keys || !sumspec || !dirty || !thresholds || fundamental_idx_hi != L.fu || !as_dev(powerspectrum))
+        return RADPUL_EVAL;
+    LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
+    // demod_binary_hs_cpu.c:73-83: zero the summed spectra and the page flags, alias sumspec[0] to the spectrum
+    for (int i = 1; i < 5; i++) memset(sumspec[i], 0, fundamental_idx_hi * sizeof(float));
+    for (int i = 0; i < 5; i++) memset(dirty[i], 0, nr_pages * sizeof(int32_t));
+    BrpGeomDev g = L.gd;
+    g.w2 = window_2;
+    g.fu = fundamental_idx_hi;
+    g.h = harmonic_idx_hi;
+    BrpThresholds t;
+    for (int k = 0; k < 5; k++) t.t[k] = thresholds[k];
+    LG_TRY(cudaMemsetAsync(L.d_keys, 0, sizeof(unsigned long long) * L.hit_cap, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(cudaMemsetAsync(L.d_hit_counter, 0, sizeof(uint32_t), L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(brp_launch_harmonic_summing(as_dev(powerspectrum), 0, 1, g, t, 0, L.d_keys, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(brp_launch_collect(L.d_keys, fundamental_idx_hi, 0, L.d_hits, L.hit_cap, L.d_hit_counter, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    uint32_t n = 0;
+    LG_TRY(cudaMemcpyAsync(&n, L.d_hit_counter, sizeof(uint32_t), cudaMemcpyDeviceToHost, L.stream), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
+    LG_TRY(cudaMemcpyAsync(L.h_spectrum, as_dev(powerspectrum), sizeof(float) * fundamental_idx_hi, cudaMemcpyDeviceToHost, L.stream),
+           RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
+    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    if (n) {
+        LG_TRY(cudaMemcpy(L.h_hits, L.d_hits, sizeof(brp_hit) * n, cudaMemcpyDeviceToHost), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
+    }
+    sumspec[0] = L.h_spectrum;
+    for (uint32_t i = 0; i < n; i++) {
+        const brp_hit &h = L.h_hits[i];
+        if (h.harm_idx > 0) sumspec[h.harm_idx][h.bin] = h.power;
+        dirty[h.harm_idx][h.bin >> BRP_LOG_PS_PAGE_SIZE] = 1;
+    }
+    return 0;
+}
+
+int tear_down_harmonic_summing(float **sumspec, int32_t **dirty)
+{
+    if (sumspec)
+        for (int i = 1; i < 5; i++) { free(sumspec[i]); sumspec[i] = NULL; }
+    if (dirty)
+        for (int i = 0; i < 5; i++) { free(dirty[i]); dirty[i] = NULL; }
+    if (!L.initialised) return 0;
+    cudaSetDevice(L.device);
+    cudaFree(L.d_keys); cudaFree(L.d_hits); cudaFree(L.d_hit_counter); cudaFreeHost(L.h_hits); cudaFreeHost(L.h_spectrum);
+    L.d_keys = NULL; L.d_hits = NULL; L.d_hit_counter = NULL; L.h_hits = NULL; L.h_spectrum = NULL;
+    return 0;
+}
+
+} // extern "C"

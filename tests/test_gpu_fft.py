@@ -1,0 +1,107 @@
+"""GPU parity, tap 2a: hand-written two-pass FFT + power epilogue against the oracle's double-precision DFT.
+Tolerance (north_star / SURVEY.md 8c): |a-b| <= 1e-4 * max(|b|, <P>).  Full-size checks use size-independent
+properties (impulse, tone, Parseval, linearity of the amplitude spectrum)."""
+import numpy as np
+import pytest
+
+import brp_b200
+from brp_b200 import synth
+from helpers import GOLDEN_TEMPLATES, golden_series_AB, power_close
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4
+
+
+def _search(n, padding=1.0, window=100):
+    nu = int(round(n / padding))
+    g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, padding, 400.0, window)
+    assert g.nsamples == n
+    return brp_b200.Search(g, max_batch=1), g
+
+
+@pytest.mark.parametrize("n", [1 << 9, 1 << 10, 1 << 12, 1 << 13, 1 << 14, 1 << 15, 1 << 16, 1 << 17, 1 << 18, 1 << 19, 1 << 20, 1 << 21])
+def test_spectrum_matches_oracle_pow2(oracle, n):
+    s, g = _search(n, window=10)
+    x = np.random.default_rng(n).standard_normal(n).astype(np.float32)
+    got = s.stage_spectrum_of(x)
+    want = oracle.power_spectrum(x, n)
+    err, _ = power_close(got, want, RTOL)
+    assert err <= RTOL, err
+    assert got[0] == 0.0
+    # much tighter in the mean: a float32 FFT should sit near 1e-6
+    rel = np.linalg.norm(got.astype(np.float64) - want) / np.linalg.norm(want)
+    assert rel < 2e-6, rel
+    s.close()
+
+
+@pytest.mark.parametrize("n", [3 << 9, 3 << 11, 3 << 12, 3 << 14, 3 << 15, 3 << 17, 3 << 20])
+def test_spectrum_matches_oracle_3x(oracle, n):
+    s, g = _search(n, padding=3.0, window=10)
+    x = np.random.default_rng(n).standard_normal(n).astype(np.float32)
+    got = s.stage_spectrum_of(x)
+    want = oracle.power_spectrum(x, n)
+    err, _ = power_close(got, want, RTOL)
+    assert err <= RTOL, err
+    rel = np.linalg.norm(got.astype(np.float64) - want) / np.linalg.norm(want)
+    assert rel < 2e-6, rel
+    s.close()
+
+
+def test_unsupported_length_is_rejected():
+    g = brp_b200.derive_geometry(5 << 12, synth.TSAMPLE_US, 1.0, 400.0, 10)
+    with pytest.raises(brp_b200.BrpError) as e:
+        brp_b200.Search(g, max_batch=1)
+    assert e.value.code == brp_b200.RADPUL_CUDA_FFT_PLAN
+
+
+@pytest.mark.parametrize("tag,padding", [("A", 1.0), ("B", 3.0)])
+def test_resample_then_spectrum_matches_golden(golden, tag, padding):
+    """Mean padding applied on load by the FFT's first pass == the reference's materialised padding."""
+    series = golden_series_AB()
+    g = brp_b200.derive_geometry(1 << 14, synth.TSAMPLE_US, padding, 400.0, 200)
+    s = brp_b200.Search(g, max_batch=2)
+    s.set_series(series)
+    for it, row in enumerate(GOLDEN_TEMPLATES):
+        t = brp_b200.derive_template(*row, g.step_inv)
+        s.stage_resample(t, want_series=False, want_index=False)
+        got = s.stage_spectrum()
+        err, _ = power_close(got, golden[f"{tag}{it}_ps"], RTOL)
+        assert err <= RTOL, (tag, it, err)
+    s.close()
+
+
+@pytest.mark.parametrize("n", [1 << 22, 3 << 22, 1 << 23])
+def test_full_size_properties(n):
+    padding = 3.0 if n % 3 == 0 else 1.0
+    s, g = _search(n, padding=padding, window=1000)
+    f = g.fft_size
+    # impulse: |X_k| = 1 for every k  ->  P = 1/N
+    x = np.zeros(n, np.float32)
+    x[12345] = 1.0
+    got = s.stage_spectrum_of(x)
+    assert got[0] == 0.0 and np.allclose(got[1:], 1.0 / n, rtol=2e-5, atol=0)
+    # pure tone on a bin: all power in that bin, P = A^2 N / 4
+    k0 = 1234567
+    t = np.arange(n, dtype=np.float64)
+    x = (0.5 * np.cos(2 * np.pi * k0 * t / n + 0.3)).astype(np.float32)
+    got = s.stage_spectrum_of(x)
+    assert abs(got[k0] - 0.25 * n / 4) <= 1e-4 * 0.25 * n / 4
+    rest = np.delete(got, k0)
+    assert rest.max() < 1e-6 * got[k0]
+    # Parseval on noise: sum_k P_k (k=1..F-1, interior bins counted twice) = sum x^2 - (DC and Nyquist terms)
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal(n).astype(np.float32)
+    x -= np.float32(x.mean(dtype=np.float64))
+    got = s.stage_spectrum_of(x).astype(np.float64)
+    total = 2.0 * got[1:f - 1].sum() + got[f - 1]
+    want = float(np.sum(x.astype(np.float64) ** 2)) - float(np.sum(x.astype(np.float64))) ** 2 / n
+    assert abs(total - want) <= 2e-6 * want
+    # spot-check 64 bins against a direct double-precision DFT
+    ks = rng.integers(1, f, 64)
+    xd = x.astype(np.float64)
+    for k in ks[:16]:
+        ph = np.exp(-2j * np.pi * ((k * np.arange(n, dtype=np.int64)) % n) / n)
+        want_k = abs(np.dot(xd, ph)) ** 2 / n
+        assert abs(got[k] - want_k) <= 1e-4 * max(want_k, 1.0)
+    s.close()

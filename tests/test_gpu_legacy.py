@@ -1,0 +1,83 @@
+"""GPU parity through the reference's own backend interface (the drop-in boundary): the eleven legacy
+functions driven with the reference's call sequence and fed-back thresholds (demod_binary.c:1268-1293), the driver's
+candidate scan (:1310-1397) supplied by the oracle's restatement of it."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import brp_b200
+from brp_b200 import synth
+from helpers import golden_case_C, power_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _drive(oracle, series, g, go, bank, fA):
+    be = brp_b200.LegacyBackend()
+    be.set_up(series, g)
+    from oracle.oracle import CAND_DTYPE
+    cands = np.zeros(500, CAND_DTYPE)
+    tidx = np.full(500, -1, np.int32)
+    base = brp_b200.base_thresholds(fA, g.fft_size)
+    taps = []
+    for it, row in enumerate(bank):
+        t = brp_b200.derive_template(*row, g.step_inv)
+        thrA = np.maximum(base, cands["power"][99::100].astype(np.float32))      # demod_binary.c:1276-1281
+        ss, dd = be.run_template(t, thrA)
+        taps.append(([a.copy() for a in ss], [d.copy() for d in dd], thrA.copy()))
+        sp = (ctypes.POINTER(ctypes.c_float) * 5)(*[ss[k].ctypes.data_as(ctypes.POINTER(ctypes.c_float)) for k in range(5)])
+        dp = (ctypes.POINTER(ctypes.c_int32) * 5)(*[dd[k].ctypes.data_as(ctypes.POINTER(ctypes.c_int32)) for k in range(5)])
+        to = oracle.template(*row, go.step_inv)
+        oracle.L.brp_oracle_toplist_update(cands.ctypes.data_as(ctypes.c_void_p), tidx.ctypes.data_as(ctypes.c_void_p), sp, dp,
+                                           ctypes.c_uint32(g.nr_pages), ctypes.byref(go), thrA.ctypes.data_as(ctypes.c_void_p),
+                                           ctypes.byref(to), ctypes.c_int32(it))
+    be.shutdown()
+    return cands, tidx, taps
+
+
+@pytest.mark.parametrize("tag,padding", [("C1", 1.0), ("C3", 3.0)])
+def test_legacy_interface_reproduces_reference_candidates(oracle, golden, tag, padding):
+    series, _ = golden_case_C()
+    bank = golden["C_bank"]
+    g = brp_b200.derive_geometry(1 << 16, synth.TSAMPLE_US, padding, 400.0, 200)
+    go = oracle.geometry(1 << 16, synth.TSAMPLE_US, padding, 400.0, 200)
+    cands, tidx, taps = _drive(oracle, series, g, go, bank, 0.08)
+    want, want_t = oracle.search(series, go, 0.08, bank)
+    for k in range(5):
+        sl = slice(100 * k, 100 * k + 100)
+        a = sorted(zip(tidx[sl], cands["f0"][sl], cands["n_harm"][sl]))
+        b = sorted(zip(want_t[sl], want["f0"][sl], want["n_harm"][sl]))
+        assert a == b
+        pa = dict(zip(zip(tidx[sl], cands["f0"][sl]), cands["power"][sl]))
+        pb = dict(zip(zip(want_t[sl], want["f0"][sl]), want["power"][sl]))
+        for key, p in pb.items():
+            assert abs(pa[key] - p) <= 1e-4 * max(p, 1e-30)
+    # same batched result
+    bc, bt = brp_b200.search_bank(series, g, bank, fA=0.08, max_batch=4)
+    assert bc.tobytes() == cands.view(brp_b200.CAND_DTYPE).tobytes() and np.array_equal(bt, tidx)
+    # the spectrum handed out as sumspec[0] and the page flags of the last template
+    ss, dd, thrA = taps[-1]
+    t = oracle.template(*bank[-1], go.step_inv)
+    res, _, _, _ = oracle.resample(series, go, t)
+    ps = oracle.power_spectrum(res, go.nsamples)
+    err, _ = power_close(ss[0], ps[: g.fundamental_idx_hi])
+    assert err <= 1e-4
+    rss, rdirty = oracle.harmonic_summing(ps, go, thrA)
+    for k in range(5):
+        ref = ps[: g.fundamental_idx_hi] if k == 0 else rss[k - 1]
+        above = np.nonzero(ref > thrA[k] * np.float32(1.001))[0]
+        assert np.all(dd[k][above >> 10] == 1)
+        if k:
+            e, _ = power_close(ss[k][above], ref[above])
+            assert e <= 1e-4
+
+
+def test_legacy_error_codes():
+    be = brp_b200.LegacyBackend()
+    series, _ = synth.make_series(5 << 10, seed=3)
+    g = brp_b200.derive_geometry(5 << 10, synth.TSAMPLE_US, 1.0, 400.0, 20)
+    with pytest.raises(brp_b200.BrpError) as e:       # FFT length 5*2^10: only 2^a and 3*2^a are supported
+        be.set_up(series, g)
+    assert e.value.code == brp_b200.RADPUL_CUDA_FFT_PLAN
+    be.shutdown()
