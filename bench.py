@@ -157,7 +157,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    print(json.dumps(line, default=float))
 
 
 # --------------------------------------------------------------------------------------------------- our arm
@@ -309,7 +309,7 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line))
+        print(json.dumps(line, default=float))
 
 
 def main():

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 
 def _spectrum(rng, n, lines=8):
     ps = rng.exponential(1.0, n).astype(np.float32)     # chi^2_2 / 2: the null distribution of a normalised periodogram
-    for k in rng.integers(600, n // 17, lines):           # a few strong lines with harmonics
+    for k in rng.integers(n // 60, n // 17, lines):           # a few strong lines with harmonics
         for h in range(1, 17):
             ps[min(k * h, n - 1)] += np.float32(rng.uniform(3, 15))
     ps[0] = 0.0
