@@ -242,6 +242,31 @@ int brp_stage_harmonic_summing(brp_search *s, const float *host_ps, const float 
 int brp_stage_sin_lut(int device, const float *x, float *sin_out, uint32_t n);
 int brp_stage_round_index(int device, const float *f, int32_t *idx_out, uint32_t n);
 
+/* =====================================================================================
+ * 4. Resampling without any device allocation
+ * ===================================================================================== */
+
+/* No counterpart in the reference (every reference backend allocates its own scratch at set-up time).
+ *
+ * Resamples one template like run_resampling / brp_stage_resample, for callers that cannot allocate device
+ * memory when they need it: a task admitted with a fixed device-memory budget (a failed mid-run allocation
+ * costs a BOINC task a 15-minute back-off), a host that has given the whole card to its own arena, or a loop
+ * that cannot take the device-wide synchronisation of cudaMalloc/cudaFree.  This call performs no cudaMalloc,
+ * cudaFree or other allocating call.  The caller passes every buffer, all in DEVICE memory of the current
+ * device: d_series (nsamples_unpadded floats, in), d_out (nsamples floats, 16-byte aligned, out: resampled
+ * series with the mean padding), d_n_steps and d_mean (one element each, out).  `t` is a host struct
+ * (brp_derive_template), `stream` a cudaStream_t (NULL = default stream); the work is enqueued, not awaited.
+ *
+ * The kernel's scratch is a fixed array of BRP_NOALLOC_SCRATCH_BYTES inside the library image, held by every
+ * GPU that loads the library until the process exits; series longer than BRP_NOALLOC_MAX_SAMPLES are
+ * rejected with RADPUL_EVAL and a message.  The first call on a GPU looks the array's address up once; issue
+ * that first call before beginning any stream capture.  All calls on a GPU share the array: calls that may
+ * overlap on the device (different streams or threads) race and must be ordered by the caller. */
+#define BRP_NOALLOC_MAX_SAMPLES (1u << 24)
+#define BRP_NOALLOC_SCRATCH_BYTES (8u * (BRP_NOALLOC_MAX_SAMPLES / 4096u) + 256u)
+int brp_resample_noalloc(const void *d_series, uint32_t nsamples_unpadded, uint32_t nsamples, const brp_template *t,
+                         float dt, float step_inv, void *d_out, uint32_t *d_n_steps, float *d_mean, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
