@@ -190,10 +190,12 @@ __device__ __forceinline__ int pos_of_freq(int k)
 
 enum { MAP_ROW_FAST = 0, MAP_BF_FAST = 1 };
 
-// One DIF stage over the whole tile.  Load(row, pos) supplies the R inputs of a butterfly, Store(row, pos, value)
-// consumes its outputs (already multiplied by the stage twiddle W_n^{p q}).
+// One DIF stage over the whole tile.  The I/O objects are used as
+//     auto c = io.begin(row, base);   io.get(c, off);   io.put(c, off, q, value);
+// where base = blk*n + p is the butterfly's first position and off = j*S is a compile-time constant after
+// unrolling, so all per-element address arithmetic folds into immediates.
 template <int L, int ROWS, int STAGE, int MAP, typename Load, typename Store>
-__device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, Load load, Store store)
+__device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store)
 {
     constexpr int R = cfg_radix(L, STAGE);
     constexpr int n = cfg_n(L, STAGE);
@@ -202,8 +204,10 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, Load l
     constexpr int ITEMS = ROWS * BF;
     constexpr bool LAST = (STAGE == cfg_stages(L) - 1);
     constexpr int TWO = cfg_tw_offset(L, STAGE);
-#pragma unroll 1
-    for (int item = threadIdx.x; item < ITEMS; item += kThreads) {
+    static_assert(ITEMS % kThreads == 0, "tile must be a whole number of butterflies per thread");
+#pragma unroll
+    for (int it = 0; it < ITEMS / kThreads; ++it) {
+        const int item = threadIdx.x + it * kThreads;
         int row, bf;
         if (MAP == MAP_ROW_FAST) {
             row = item % ROWS;
@@ -215,24 +219,31 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, Load l
         const int blk = bf / S, p = bf % S;
         const int base = blk * n + p;
         float2 v[R];
+        const auto lc = load.begin(row, base);
 #pragma unroll
-        for (int j = 0; j < R; ++j) v[j] = load(row, base + j * S);
+        for (int j = 0; j < R; ++j) v[j] = load.get(lc, j * S);
         Dft<R>::run(v);
+        const auto sc = store.begin(row, base);
+        const float2 *__restrict__ twp = tw + TWO + p;
 #pragma unroll
         for (int q = 0; q < R; ++q) {
             float2 o = v[out_slot<R>(q)];
-            if (!LAST && q > 0) o = cmul(o, __ldg(&tw[TWO + (q - 1) * S + p]));
-            store(row, base + q * S, o);
+            if (!LAST && q > 0) o = cmul(o, __ldg(twp + (q - 1) * S));
+            store.put(sc, q * S, q, o);
         }
     }
 }
 
+// Shared-memory tile.  phys(base + off) == phys(base) + phys(off) for every (base, off) a stage produces:
+// off = j*S with S a power of two, base = blk*R*S + p with p < S, so neither the /16 nor the /256 padding
+// term carries from the p part into the j part (S | 16 or 16 | S, S | 256 or 256 | S).
 template <int L, int ROWS>
 struct SmemIO {
     float2 *sm;
     static constexpr int PITCH = cfg_pitch(L, ROWS);
-    __device__ __forceinline__ float2 operator()(int row, int pos) const { return sm[row * PITCH + phys(pos)]; }
-    __device__ __forceinline__ void operator()(int row, int pos, float2 v) const { sm[row * PITCH + phys(pos)] = v; }
+    __device__ __forceinline__ float2 *begin(int row, int base) const { return sm + row * PITCH + phys(base); }
+    __device__ __forceinline__ float2 get(float2 *c, int off) const { return c[phys(off)]; }
+    __device__ __forceinline__ void put(float2 *c, int off, int, float2 v) const { c[phys(off)] = v; }
 };
 
 // middle stages (shared -> shared), recursively unrolled over the stage index
@@ -248,44 +259,96 @@ __device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm)
 }
 
 // ------------------------------------------------------------------ pass 1
+// first stage: column `col` of the M2 x M1 view, element m2 = pos  ->  z = (x[2c], x[2c+1]), c = pos*M1 + col
+template <int L>
+struct Pass1Load {
+    const float *x;
+    uint32_t m1, col0, n_steps;
+    float mean;
+    struct Ctx {
+        const float *p;
+        uint32_t i0;
+        bool valid, fast;
+    };
+    __device__ __forceinline__ Ctx begin(int row, int base) const
+    {
+        constexpr int R = cfg_radix(L, 0), S = cfg_stride(L, 0);
+        Ctx c;
+        const uint32_t col = col0 + row;
+        c.valid = col < m1;
+        c.i0 = 2u * ((uint32_t)base * m1 + col);
+        c.p = x + c.i0;
+        // whole butterfly below n_steps: no per-element padding test
+        c.fast = c.valid && (c.i0 + 2u * (uint32_t)((R - 1) * S) * m1 + 1u < n_steps);
+        return c;
+    }
+    __device__ __forceinline__ float2 get(const Ctx &c, int off) const
+    {
+        const uint32_t d = 2u * (uint32_t)off * m1;
+        if (c.fast) return *reinterpret_cast<const float2 *>(c.p + d);
+        if (!c.valid) return make_float2(0.f, 0.f);
+        // mean padding on load (demod_binary_resamp_cpu.c:130-133): samples >= n_steps take the series mean
+        const uint32_t i = c.i0 + d;
+        if (i + 1 < n_steps) return *reinterpret_cast<const float2 *>(c.p + d);
+        return make_float2(i < n_steps ? c.p[d] : mean, mean);
+    }
+};
+
+// last stage: output k2 = kb + q*(L/R) of column col, times the inter-pass twiddle
+//     W_M^{col*k2} = W_M^{col*kb} * W_{M1*R}^{col*q}
+// first factor: one exact-argument sincospi per butterfly (col*kb < M); second factor: table tb[col][q]
+// generated in double precision.  Stored transposed: Y[k2][col].
+template <int L>
+struct Pass1Store {
+    float2 *y;
+    const float2 *tb;
+    uint32_t m1, col0;
+    float inv_m;
+    static constexpr int RL = cfg_radix(L, cfg_stages(L) - 1);
+    struct Ctx {
+        float2 *p;
+        const float2 *t;
+        float2 a;
+        bool valid;
+    };
+    __device__ __forceinline__ Ctx begin(int row, int base) const
+    {
+        Ctx c;
+        const uint32_t col = col0 + row;
+        c.valid = col < m1;
+        const uint32_t kb = (uint32_t)freq_of_pos<L>(base);
+        c.p = y + (size_t)kb * m1 + col;
+        c.t = tb + (size_t)col * RL;
+        float sn, cs;
+        sincospif(-2.0f * (float)(col * kb) * inv_m, &sn, &cs);
+        c.a = make_float2(cs, sn);
+        return c;
+    }
+    __device__ __forceinline__ void put(const Ctx &c, int, int q, float2 v) const
+    {
+        if (!c.valid) return;
+        const float2 w = (q == 0) ? c.a : cmul(c.a, __ldg(c.t + q));
+        c.p[(size_t)q * (L / RL) * m1] = cmul(v, w);
+    }
+};
+
 template <int L, int ROWS>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t *__restrict__ n_steps_arr,
                  const float *__restrict__ mean_arr, float2 *__restrict__ work, uint32_t m1, uint32_t m,
-                 const float2 *__restrict__ tw)
+                 const float2 *__restrict__ tw, const float2 *__restrict__ tb)
 {
     extern __shared__ float2 sm[];
     constexpr int NS = cfg_stages(L);
     const int b = blockIdx.y;
     const uint32_t col0 = blockIdx.x * ROWS;
-    const float *x = in + (size_t)b * in_stride;
-    const uint32_t n_steps = n_steps_arr[b];
-    const float mean = mean_arr[b];
-    float2 *y = work + (size_t)b * m;
-    SmemIO<L, ROWS> io{sm};
-
-    auto gload = [&](int row, int pos) -> float2 {
-        const uint32_t col = col0 + row;
-        if (col >= m1) return make_float2(0.f, 0.f);
-        const uint32_t i = 2u * ((uint32_t)pos * m1 + col);
-        if (i + 1 < n_steps) return *reinterpret_cast<const float2 *>(x + i);
-        // mean padding on load (demod_binary_resamp_cpu.c:130-133): samples >= n_steps take the series mean
-        return make_float2(i < n_steps ? x[i] : mean, mean);
-    };
-    const float inv_m = 1.0f / (float)m;
-    auto gstore = [&](int row, int pos, float2 v) {
-        const uint32_t col = col0 + row;
-        if (col >= m1) return;
-        const uint32_t k2 = (uint32_t)freq_of_pos<L>(pos);
-        // inter-pass twiddle W_M^{col*k2}; col*k2 < M so the angle -2*pi*(col*k2)/M is reduced exactly
-        float sn, cs;
-        sincospif(-2.0f * (float)(col * k2) * inv_m, &sn, &cs);
-        y[(size_t)k2 * m1 + col] = cmul(v, make_float2(cs, sn));
-    };
+    const Pass1Load<L> gload{in + (size_t)b * in_stride, m1, col0, n_steps_arr[b], mean_arr[b]};
+    const Pass1Store<L> gstore{work + (size_t)b * m, tb, m1, col0, 1.0f / (float)m};
 
     if constexpr (NS == 1) {
         tile_stage<L, ROWS, 0, MAP_ROW_FAST>(tw, gload, gstore);
     } else {
+        SmemIO<L, ROWS> io{sm};
         tile_stage<L, ROWS, 0, MAP_ROW_FAST>(tw, gload, io);
         __syncthreads();
         tile_middle<L, ROWS, 1, NS - 1>(tw, sm);
@@ -294,8 +357,25 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
 }
 
 // ------------------------------------------------------------------ pass 2 + untangle + power
+// tile rows: r < T2 -> k2 = a + r ; r >= T2 -> k2 = (m2 - (a + r - T2)) mod m2 (the mirror row).
+// Only rows k2 <= m2/2 (and their mirrors) are owned by a block; the grid covers k2 = 0..m2/2.
 template <int L, int ROWS>
-__global__ void __launch_bounds__(kThreads)
+struct Pass2Load {
+    const float2 *y;
+    uint32_t a, m2;
+    __device__ __forceinline__ const float2 *begin(int row, int base) const
+    {
+        constexpr int T2 = ROWS / 2;
+        const uint32_t f = a + (uint32_t)(row < T2 ? row : row - T2);
+        if (2 * f > m2) return nullptr;
+        const uint32_t k2 = row < T2 ? f : (m2 - f) % m2;
+        return y + (size_t)k2 * L + base;
+    }
+    __device__ __forceinline__ float2 get(const float2 *c, int off) const { return c ? c[off] : make_float2(0.f, 0.f); }
+};
+
+template <int L, int ROWS>
+__global__ void __launch_bounds__(kThreads, 2)
 fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
                  uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
                  const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
@@ -306,24 +386,9 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
     constexpr uint32_t M1 = L;
     const int b = blockIdx.y;
     const uint32_t a = blockIdx.x * T2;
-    const float2 *y = work + (size_t)b * m;
     float *P = ps + (size_t)b * ps_stride;
     SmemIO<L, ROWS> io{sm};
-
-    // tile rows: r < T2 -> k2 = a + r ; r >= T2 -> k2 = (m2 - (a + r - T2)) mod m2 (the mirror row).
-    // Only rows k2 <= m2/2 (and their mirrors) are owned by a block; the grid covers k2 = 0..m2/2.
-    auto row_k2 = [&](int row) -> uint32_t {
-        const uint32_t f = a + (uint32_t)(row < T2 ? row : row - T2);
-        return row < T2 ? f : (m2 - f) % m2;
-    };
-    auto row_needed = [&](int row) -> bool {
-        const uint32_t f = a + (uint32_t)(row < T2 ? row : row - T2);
-        return 2 * f <= m2;
-    };
-    auto gload = [&](int row, int pos) -> float2 {
-        if (!row_needed(row)) return make_float2(0.f, 0.f);
-        return y[(size_t)row_k2(row) * M1 + pos];
-    };
+    const Pass2Load<L, ROWS> gload{work + (size_t)b * m, a, m2};
 
     tile_stage<L, ROWS, 0, MAP_BF_FAST>(tw, gload, io);
     __syncthreads();
@@ -333,6 +398,7 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
     // (k1' = (M1-k1) mod M1 on the self-mirrored row k2 = 0).
     //   E = (Z[k] + conj Z[M-k])/2,  O = (Z[k] - conj Z[M-k])/(2i)
     //   X[k] = E + W_N^k O,  X[M-k] = conj(E - W_N^k O)            (N = 2M)
+#pragma unroll 4
     for (int item = threadIdx.x; item < T2 * (int)M1; item += kThreads) {
         const int r = item % T2;
         const uint32_t k1 = item / T2;
@@ -346,8 +412,8 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
             if (2 * k2 == m2 && k1 >= M1 / 2) continue; // row m2/2 mirrors onto itself
             k1m = M1 - 1 - k1;
         }
-        const float2 za = io(r, pos_of_freq<L>((int)k1));
-        const float2 zb = io(r + T2, pos_of_freq<L>((int)k1m));
+        const float2 za = *io.begin(r, pos_of_freq<L>((int)k1));
+        const float2 zb = *io.begin(r + T2, pos_of_freq<L>((int)k1m));
         const float2 e = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
         const float2 d = make_float2(0.5f * (za.x - zb.x), 0.5f * (za.y + zb.y));
         const float2 o = make_float2(d.y, -d.x);
@@ -362,12 +428,13 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
 }
 
 // ------------------------------------------------------------------ host side
-typedef void (*pass1_fn)(const float *, size_t, const uint32_t *, const float *, float2 *, uint32_t, uint32_t, const float2 *);
+typedef void (*pass1_fn)(const float *, size_t, const uint32_t *, const float *, float2 *, uint32_t, uint32_t, const float2 *,
+                         const float2 *);
 typedef void (*pass2_fn)(const float2 *, float *, size_t, uint32_t, uint32_t, uint32_t, float, const float2 *, const float2 *,
                          const float2 *);
 
 struct TileInfo {
-    int L, rows, smem, tw_size;
+    int L, rows, smem, tw_size, last_radix;
     pass1_fn p1;
     pass2_fn p2;
 };
@@ -381,6 +448,7 @@ TileInfo make_info()
     t.rows = ROWS;
     t.smem = ROWS * cfg_pitch(L, ROWS) * (int)sizeof(float2);
     t.tw_size = cfg_tw_size(L);
+    t.last_radix = cfg_radix(L, cfg_stages(L) - 1);
     t.p1 = fft_pass1_kernel<L, ROWS>;
     t.p2 = fft_pass2_kernel<L, ROWS>;
     return t;
@@ -459,6 +527,14 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
     p->tw_pass1 = upload(tw);
     gen_tile_tw_dispatch(m1, tw);
     p->tw_pass2 = upload(tw);
+    // second factor of the inter-pass twiddle: tb[col][q] = exp(-2 pi i col q / (m1 * R_last))
+    tw.resize((size_t)m1 * t1->last_radix);
+    for (uint32_t col = 0; col < m1; ++col)
+        for (int q = 0; q < t1->last_radix; ++q) {
+            const double ang = -2.0 * M_PI * (double)((unsigned long long)col * q) / ((double)m1 * t1->last_radix);
+            tw[(size_t)col * t1->last_radix + q] = make_float2((float)cos(ang), (float)sin(ang));
+        }
+    p->tw_inter_hi = upload(tw);
     tw.resize(m2);
     for (uint32_t k = 0; k < m2; ++k) {
         const double ang = -2.0 * M_PI * (double)k / (double)n;
@@ -471,7 +547,7 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
         tw[k] = make_float2((float)cos(ang), (float)sin(ang));
     }
     p->tw_untangle_b = upload(tw);
-    if (!p->tw_pass1 || !p->tw_pass2 || !p->tw_untangle_a || !p->tw_untangle_b) {
+    if (!p->tw_pass1 || !p->tw_pass2 || !p->tw_untangle_a || !p->tw_untangle_b || !p->tw_inter_hi) {
         brp_fft_plan_destroy(p);
         return RADPUL_CUDA_MEM_ALLOC_DEVICE;
     }
@@ -500,7 +576,7 @@ cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
-    t1->p1<<<g1, kThreads, t1->smem, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1);
+    t1->p1<<<g1, kThreads, t1->smem, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (mid_event) cudaEventRecord(mid_event, st);
