@@ -78,14 +78,22 @@ __host__ __device__ constexpr int cfg_tw_offset(int L, int s)
 }
 __host__ __device__ constexpr int cfg_tw_size(int L) { return cfg_tw_offset(L, cfg_stages(L)); }
 
-__host__ __device__ constexpr int phys(int pos) { return pos + (pos >> 4) + (pos >> 8); }
-// row pitch: phys(L) rounded up so that (pitch mod 16) spreads ROWS rows over the 16 eight-byte banks
-__host__ __device__ constexpr int cfg_pitch(int L, int rows)
-{
-    const int want = rows >= 16 ? 1 : 16 / rows;
-    const int base = phys(L);
-    return base + ((want - base % 16) + 16) % 16;
-}
+// Shared-memory layout of a tile: element `pos` of row `row` lives at row*PITCH + pos + pos/16 + C8*(pos/256)
+// (float2 units).  The padding constants, the pitch residue and the lane permutation of the row-fast stages were
+// chosen per tile shape with tools/bank_conflicts.py, which replays every shared-memory access of the transform:
+// with these values all stages of the production shapes are conflict-free (pass 1: 2048x4, pass 2: 1024x8 incl.
+// the digit-reversed reads of the untangle epilogue).
+template <int L, int ROWS, int PASS>
+struct Layout {
+    static constexpr int C8 = (PASS == 2 && (L == 2048 || L == 4096)) ? 1 : 0;
+    static constexpr int EXTRA = PASS == 2 ? (L == 2048 ? 4 : (L == 4096 || L == 16) ? 0 : 1)
+                                           : (ROWS == 4 ? (L % 3 == 0 ? 1 : 2) : ROWS == 2 ? (L == 4096 ? 8 : 4) : 1);
+    // permute the low four bits of the butterfly index in the first (global -> shared) stage of pass 1
+    static constexpr bool ROT0 = PASS == 1 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
+    __host__ __device__ static constexpr int phys(int pos) { return pos + (pos >> 4) + C8 * (pos >> 8); }
+    static constexpr int PITCH = phys(L) + EXTRA;
+    static constexpr int BYTES = ROWS * PITCH * 8;
+};
 __host__ __device__ constexpr int cfg_rows(int L)
 {
     const int tile = (L % 3 == 0) ? 12288 : 8192;
@@ -93,8 +101,9 @@ __host__ __device__ constexpr int cfg_rows(int L)
 }
 
 // ------------------------------------------------------------------ complex helpers
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// Blackwell packed FP32x2 arithmetic (FADD2 / FFMA2): one instruction per complex add or subtract
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a); }
 __device__ __forceinline__ float2 cmul(float2 a, float2 b)
 {
     return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
@@ -194,7 +203,7 @@ enum { MAP_ROW_FAST = 0, MAP_BF_FAST = 1 };
 //     auto c = io.begin(row, base);   io.get(c, off);   io.put(c, off, q, value);
 // where base = blk*n + p is the butterfly's first position and off = j*S is a compile-time constant after
 // unrolling, so all per-element address arithmetic folds into immediates.
-template <int L, int ROWS, int STAGE, int MAP, typename Load, typename Store>
+template <int L, int ROWS, int STAGE, int MAP, bool ROT, typename Load, typename Store>
 __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store)
 {
     constexpr int R = cfg_radix(L, STAGE);
@@ -212,6 +221,8 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
         if (MAP == MAP_ROW_FAST) {
             row = item % ROWS;
             bf = item / ROWS;
+            // same set of butterflies, different lane order: spreads a half-warp's shared-memory stores over all banks
+            if (ROT && BF >= 16) bf = (bf & ~15) | ((bf & 1) << 3) | ((bf >> 1) & 7);
         } else {
             row = item / BF;
             bf = item % BF;
@@ -237,24 +248,24 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
 // Shared-memory tile.  phys(base + off) == phys(base) + phys(off) for every (base, off) a stage produces:
 // off = j*S with S a power of two, base = blk*R*S + p with p < S, so neither the /16 nor the /256 padding
 // term carries from the p part into the j part (S | 16 or 16 | S, S | 256 or 256 | S).
-template <int L, int ROWS>
+template <int L, int ROWS, int PASS>
 struct SmemIO {
+    using Lay = Layout<L, ROWS, PASS>;
     float2 *sm;
-    static constexpr int PITCH = cfg_pitch(L, ROWS);
-    __device__ __forceinline__ float2 *begin(int row, int base) const { return sm + row * PITCH + phys(base); }
-    __device__ __forceinline__ float2 get(float2 *c, int off) const { return c[phys(off)]; }
-    __device__ __forceinline__ void put(float2 *c, int off, int, float2 v) const { c[phys(off)] = v; }
+    __device__ __forceinline__ float2 *begin(int row, int base) const { return sm + row * Lay::PITCH + Lay::phys(base); }
+    __device__ __forceinline__ float2 get(float2 *c, int off) const { return c[Lay::phys(off)]; }
+    __device__ __forceinline__ void put(float2 *c, int off, int, float2 v) const { c[Lay::phys(off)] = v; }
 };
 
 // middle stages (shared -> shared), recursively unrolled over the stage index
-template <int L, int ROWS, int STAGE, int END>
+template <int L, int ROWS, int PASS, int STAGE, int END>
 __device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm)
 {
     if constexpr (STAGE < END) {
-        SmemIO<L, ROWS> io{sm};
-        tile_stage<L, ROWS, STAGE, MAP_BF_FAST>(tw, io, io);
+        SmemIO<L, ROWS, PASS> io{sm};
+        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false>(tw, io, io);
         __syncthreads();
-        tile_middle<L, ROWS, STAGE + 1, END>(tw, sm);
+        tile_middle<L, ROWS, PASS, STAGE + 1, END>(tw, sm);
     }
 }
 
@@ -346,13 +357,13 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
     const Pass1Store<L> gstore{work + (size_t)b * m, tb, m1, col0, 1.0f / (float)m};
 
     if constexpr (NS == 1) {
-        tile_stage<L, ROWS, 0, MAP_ROW_FAST>(tw, gload, gstore);
+        tile_stage<L, ROWS, 0, MAP_ROW_FAST, false>(tw, gload, gstore);
     } else {
-        SmemIO<L, ROWS> io{sm};
-        tile_stage<L, ROWS, 0, MAP_ROW_FAST>(tw, gload, io);
+        SmemIO<L, ROWS, 1> io{sm};
+        tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 1>::ROT0>(tw, gload, io);
         __syncthreads();
-        tile_middle<L, ROWS, 1, NS - 1>(tw, sm);
-        tile_stage<L, ROWS, NS - 1, MAP_ROW_FAST>(tw, io, gstore);
+        tile_middle<L, ROWS, 1, 1, NS - 1>(tw, sm);
+        tile_stage<L, ROWS, NS - 1, MAP_ROW_FAST, false>(tw, io, gstore);
     }
 }
 
@@ -387,12 +398,12 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
     const int b = blockIdx.y;
     const uint32_t a = blockIdx.x * T2;
     float *P = ps + (size_t)b * ps_stride;
-    SmemIO<L, ROWS> io{sm};
+    SmemIO<L, ROWS, 2> io{sm};
     const Pass2Load<L, ROWS> gload{work + (size_t)b * m, a, m2};
 
-    tile_stage<L, ROWS, 0, MAP_BF_FAST>(tw, gload, io);
+    tile_stage<L, ROWS, 0, MAP_BF_FAST, false>(tw, gload, io);
     __syncthreads();
-    tile_middle<L, ROWS, 1, NS>(tw, sm);
+    tile_middle<L, ROWS, 2, 1, NS>(tw, sm);
 
     // ---- untangle + power.  Pair (k, M-k): Z[k] in row r at k1, Z[M-k] in row r+T2 at k1' = M1-1-k1
     // (k1' = (M1-k1) mod M1 on the self-mirrored row k2 = 0).
@@ -434,7 +445,7 @@ typedef void (*pass2_fn)(const float2 *, float *, size_t, uint32_t, uint32_t, ui
                          const float2 *);
 
 struct TileInfo {
-    int L, rows, smem, tw_size, last_radix;
+    int L, rows, smem1, smem2, tw_size, last_radix;
     pass1_fn p1;
     pass2_fn p2;
 };
@@ -446,7 +457,8 @@ TileInfo make_info()
     TileInfo t;
     t.L = L;
     t.rows = ROWS;
-    t.smem = ROWS * cfg_pitch(L, ROWS) * (int)sizeof(float2);
+    t.smem1 = Layout<L, ROWS, 1>::BYTES;
+    t.smem2 = Layout<L, ROWS, 2>::BYTES;
     t.tw_size = cfg_tw_size(L);
     t.last_radix = cfg_radix(L, cfg_stages(L) - 1);
     t.p1 = fft_pass1_kernel<L, ROWS>;
@@ -519,7 +531,7 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
     const TileInfo *t1 = find_tile(m2), *t2 = find_tile(m1);
     if (!t1 || !t2) return RADPUL_CUDA_FFT_PLAN;
     p->n = n; p->m = m; p->m1 = m1; p->m2 = m2; p->radix3 = (odd == 3);
-    p->smem_pass1 = t1->smem; p->smem_pass2 = t2->smem;
+    p->smem_pass1 = t1->smem1; p->smem_pass2 = t2->smem2;
     p->launches_per_batch = 2;
 
     std::vector<float2> tw;
@@ -551,8 +563,10 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
         brp_fft_plan_destroy(p);
         return RADPUL_CUDA_MEM_ALLOC_DEVICE;
     }
-    if (cudaFuncSetAttribute((const void *)t1->p1, cudaFuncAttributeMaxDynamicSharedMemorySize, t1->smem) != cudaSuccess ||
-        cudaFuncSetAttribute((const void *)t2->p2, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem) != cudaSuccess) {
+    // (measured: forcing the maximum shared-memory carve-out slows both passes by 15-35 %: the twiddle tables and the
+    //  short global runs live off the L1 that is left over, so the driver's default split is kept)
+    if (cudaFuncSetAttribute((const void *)t1->p1, cudaFuncAttributeMaxDynamicSharedMemorySize, t1->smem1) != cudaSuccess ||
+        cudaFuncSetAttribute((const void *)t2->p2, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem2) != cudaSuccess) {
         brp_fft_plan_destroy(p);
         return RADPUL_CUDA_FFT_PLAN;
     }
@@ -576,13 +590,13 @@ cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
-    t1->p1<<<g1, kThreads, t1->smem, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
+    t1->p1<<<g1, kThreads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (mid_event) cudaEventRecord(mid_event, st);
     const int T2 = t2->rows / 2;
     const dim3 g2((p.m2 / 2 + 1 + T2 - 1) / T2, batch); // rows k2 = 0 .. m2/2
-    t2->p2<<<g2, kThreads, t2->smem, st>>>(work, ps, ps_stride, ps_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
+    t2->p2<<<g2, kThreads, t2->smem2, st>>>(work, ps, ps_stride, ps_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
                                            p.tw_untangle_b);
     return cudaGetLastError();
 }

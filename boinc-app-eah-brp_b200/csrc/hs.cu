@@ -50,92 +50,107 @@ __device__ __forceinline__ void offer(unsigned long long *slot, float power, uin
     atomicMax(slot, ((unsigned long long)__float_as_uint(power) << 32) | tkey);
 }
 
+// stage the sixteen harmonic slices of tile (bx, template b) into `dst` with bulk async copies (called by warp 0)
+__device__ __forceinline__ void issue_tile(const float *__restrict__ ps, size_t ps_stride, const BrpGeomDev &g, uint32_t tile,
+                                           uint32_t tiles_per_template, float *dst, uint32_t bar_addr)
+{
+    const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
+    const float *__restrict__ P = ps + (size_t)b * ps_stride;
+    const uint32_t i0 = g.w2 + bx * kSpan, i1 = min(i0 + kSpan, g.h) - 1;
+    const int l = (threadIdx.x & 31) + 1;
+    uint32_t bytes = 0, first = 0;
+    if (l <= 16) {
+        first = (((uint32_t)l * i0 + 8u) >> 4) & ~3u;                    // 16-byte aligned source
+        const uint32_t last = ((uint32_t)l * i1 + 8u) >> 4;
+        bytes = (((last - first + 1u) + 3u) & ~3u) * 4u;                 // whole 16-byte units (rows are padded past H)
+    }
+    uint32_t total = bytes;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+    if ((threadIdx.x & 31) == 0)
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(total) : "memory");
+    __syncwarp();
+    if (l <= 16)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         smem_u32(dst + slice_off(l))),
+                     "l"(P + first), "r"(bytes), "r"(bar_addr)
+                     : "memory");
+}
+
+// Persistent CTAs: each loops over tiles (kSpan bins of one template) with a two-deep shared-memory ring, so the
+// bulk copies of the next tile run while the current one is summed.
 __global__ void __launch_bounds__(kHsThreads)
 harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomDev g, BrpThresholds thr,
-                        uint32_t first_template, unsigned long long *__restrict__ keys)
+                        uint32_t first_template, uint32_t tiles_per_template, uint32_t total_tiles,
+                        unsigned long long *__restrict__ keys)
 {
     extern __shared__ __align__(128) float sm[];
-    __shared__ __align__(8) unsigned long long bar;
+    __shared__ __align__(8) unsigned long long bar[2];
 
-    const float *__restrict__ P = ps + (size_t)blockIdx.y * ps_stride;
-    const uint32_t tkey = 0xFFFFFFFFu - (first_template + blockIdx.y);
     const uint32_t fu = g.fu;
-    const uint32_t i0 = g.w2 + blockIdx.x * kSpan;           // first bin of this CTA
-    const uint32_t i1 = min(i0 + kSpan, g.h) - 1;            // last bin of this CTA (i0 <= i1 by grid construction)
-
-    // ---- stage the sixteen harmonic slices with bulk async copies
-    const uint32_t bar_addr = smem_u32(&bar);
+    const uint32_t bar0 = smem_u32(&bar[0]);
     if (threadIdx.x == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (threadIdx.x < 32) {
-        const int l = threadIdx.x + 1;
-        uint32_t bytes = 0, first = 0;
-        if (l <= 16) {
-            first = ((uint32_t)l * i0 + 8u) >> 4;
-            const uint32_t last = ((uint32_t)l * i1 + 8u) >> 4;
-            first &= ~3u;                                    // 16-byte aligned source
-            bytes = (((last - first + 1u) + 3u) & ~3u) * 4u; // whole 16-byte units (the row is padded past H)
-        }
-        uint32_t total = bytes;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-        if (threadIdx.x == 0)
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(total) : "memory");
-        __syncwarp();
-        if (l <= 16) {
-            const uint32_t dst = smem_u32(sm + slice_off(l));
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                         "l"(P + first), "r"(bytes), "r"(bar_addr)
-                         : "memory");
-        }
-    }
+    uint32_t tile = blockIdx.x;
+    if (tile < total_tiles && threadIdx.x < 32) issue_tile(ps, ps_stride, g, tile, tiles_per_template, sm, bar0);
 
-    // ---- per-thread slice indices of its first bin (the only index arithmetic of the kernel)
-    const uint32_t i = i0 + threadIdx.x;
-    uint32_t idx[17];
-#pragma unroll
-    for (int l = 1; l <= 16; ++l) {
-        const uint32_t first = (((uint32_t)l * i0 + 8u) >> 4) & ~3u;
-        idx[l] = slice_off(l) + ((((uint32_t)l * i + 8u) >> 4) - first);
-    }
-    const uint32_t j1 = (8u * i + 8u) >> 4, j2 = (4u * i + 8u) >> 4, j3 = (2u * i + 8u) >> 4, j4 = (i + 8u) >> 4;
+    for (uint32_t n = 0; tile < total_tiles; tile += gridDim.x, ++n) {
+        const uint32_t st = n & 1u;
+        const uint32_t next = tile + gridDim.x;
+        // the other stage was fully consumed before the __syncthreads that ended the previous iteration
+        if (next < total_tiles && threadIdx.x < 32)
+            issue_tile(ps, ps_stride, g, next, tiles_per_template, sm + (st ^ 1u) * kSmemFloats, bar0 + 8 * (st ^ 1u));
 
-    // wait for the copies (phase 0 of the barrier)
-    {
-        uint32_t done = 0;
-        while (!done) {
-            asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n selp.u32 %0, 1, 0, p;\n}"
-                         : "=r"(done)
-                         : "r"(bar_addr)
-                         : "memory");
+        const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
+        const uint32_t tkey = 0xFFFFFFFFu - (first_template + b);
+        const uint32_t i0 = g.w2 + bx * kSpan;
+        const uint32_t i1 = min(i0 + kSpan, g.h) - 1;
+        // per-thread slice indices of its first bin (the only index arithmetic per tile)
+        const uint32_t i = i0 + threadIdx.x;
+        const float *__restrict__ buf = sm + st * kSmemFloats;
+        uint32_t idx[17];
+#pragma unroll
+        for (int l = 1; l <= 16; ++l) {
+            const uint32_t first = (((uint32_t)l * i0 + 8u) >> 4) & ~3u;
+            idx[l] = slice_off(l) + ((((uint32_t)l * i + 8u) >> 4) - first);
         }
-    }
-
+        {   // wait for this stage's copies: use number n>>1 of the barrier -> parity (n>>1)&1
+            const uint32_t parity = (n >> 1) & 1u, addr = bar0 + 8 * st;
+            uint32_t done = 0;
+            while (!done) {
+                asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                             : "=r"(done)
+                             : "r"(addr), "r"(parity)
+                             : "memory");
+            }
+        }
 #pragma unroll
-    for (int u = 0; u < kHsPerThread; ++u) {
-        const uint32_t iu = i + u * kHsThreads;
-        if (iu > i1) break;
-        // bins kHsThreads apart: slice index advances by exactly l*kHsThreads/16
-#define PH(l) sm[idx[l] + u * ((l) * kHsThreads / 16)]
-        const float s0 = PH(16);
-        const float s1 = s0 + PH(8);
-        const float s2 = s1 + (PH(12) + PH(4));
-        const float s3 = s2 + (((PH(14) + PH(10)) + PH(6)) + PH(2));
-        const float s4 = s3 + (((((((PH(15) + PH(13)) + PH(11)) + PH(9)) + PH(7)) + PH(5)) + PH(3)) + PH(1));
+        for (int u = 0; u < kHsPerThread; ++u) {
+            const uint32_t iu = i + u * kHsThreads;
+            if (iu > i1) break;
+            // bins kHsThreads apart: slice index advances by exactly l*kHsThreads/16
+#define PH(l) buf[idx[l] + u * ((l) * kHsThreads / 16)]
+            const float s0 = PH(16);
+            const float s1 = s0 + PH(8);
+            const float s2 = s1 + (PH(12) + PH(4));
+            const float s3 = s2 + (((PH(14) + PH(10)) + PH(6)) + PH(2));
+            const float s4 = s3 + (((((((PH(15) + PH(13)) + PH(11)) + PH(9)) + PH(7)) + PH(5)) + PH(3)) + PH(1));
 #undef PH
-        if ((s0 > thr.t[0]) | (s1 > thr.t[1]) | (s2 > thr.t[2]) | (s3 > thr.t[3]) | (s4 > thr.t[4])) {
-            // rare path: fundamental bins of this i (they advance by kHsThreads/2^k per step)
-            const uint32_t b0 = iu, b1 = j1 + u * (kHsThreads / 2), b2 = j2 + u * (kHsThreads / 4), b3 = j3 + u * (kHsThreads / 8),
-                           b4 = j4 + u * (kHsThreads / 16);
-            if (s0 > thr.t[0] && b0 < fu) offer(keys + b0, s0, tkey);
-            if (s1 > thr.t[1] && b1 < fu) offer(keys + (size_t)fu + b1, s1, tkey);
-            if (s2 > thr.t[2] && b2 < fu) offer(keys + 2 * (size_t)fu + b2, s2, tkey);
-            if (s3 > thr.t[3] && b3 < fu) offer(keys + 3 * (size_t)fu + b3, s3, tkey);
-            if (s4 > thr.t[4] && b4 < fu) offer(keys + 4 * (size_t)fu + b4, s4, tkey);
+            if ((s0 > thr.t[0]) | (s1 > thr.t[1]) | (s2 > thr.t[2]) | (s3 > thr.t[3]) | (s4 > thr.t[4])) {
+                // rare path: fundamental bins j_k = (i*2^(4-k) + 8) >> 4 of this i
+                const uint32_t b1 = (8u * iu + 8u) >> 4, b2 = (4u * iu + 8u) >> 4, b3 = (2u * iu + 8u) >> 4, b4 = (iu + 8u) >> 4;
+                if (s0 > thr.t[0] && iu < fu) offer(keys + iu, s0, tkey);
+                if (s1 > thr.t[1] && b1 < fu) offer(keys + (size_t)fu + b1, s1, tkey);
+                if (s2 > thr.t[2] && b2 < fu) offer(keys + 2 * (size_t)fu + b2, s2, tkey);
+                if (s3 > thr.t[3] && b3 < fu) offer(keys + 3 * (size_t)fu + b3, s3, tkey);
+                if (s4 > thr.t[4] && b4 < fu) offer(keys + 4 * (size_t)fu + b4, s4, tkey);
+            }
         }
+        __syncthreads(); // everyone is done with stage `st` before it is refilled two iterations later
     }
 }
 
@@ -166,18 +181,26 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
                                         BrpThresholds thr, uint32_t first_template, unsigned long long *keys,
                                         cudaStream_t st)
 {
-    if (g.h <= g.w2) return cudaSuccess;
-    static bool configured[64]; // per device: the attribute belongs to the function on the current device
-    const int smem = kSmemFloats * (int)sizeof(float);
+    if (g.h <= g.w2 || batch <= 0) return cudaSuccess;
+    static int ctas_per_device[64]; // persistent grid size, per device (0 = not configured yet)
+    const int smem = 2 * kSmemFloats * (int)sizeof(float);
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || !configured[dev]) {
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!ctas_per_device[dev]) {
         cudaError_t e = cudaFuncSetAttribute((const void *)harmonic_summing_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) configured[dev] = true;
+        cudaFuncSetAttribute((const void *)harmonic_summing_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, harmonic_summing_kernel, kHsThreads, smem);
+        if (e != cudaSuccess) return e;
+        ctas_per_device[dev] = (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1); // one resident wave
     }
-    const dim3 grid((g.h - g.w2 + kSpan - 1) / kSpan, batch);
-    harmonic_summing_kernel<<<grid, kHsThreads, smem, st>>>(ps, ps_stride, g, thr, first_template, keys);
+    const uint32_t tiles_per_template = (g.h - g.w2 + kSpan - 1) / kSpan;
+    const uint32_t total = tiles_per_template * (uint32_t)batch;
+    const uint32_t grid = total < (uint32_t)ctas_per_device[dev] ? total : (uint32_t)ctas_per_device[dev];
+    harmonic_summing_kernel<<<grid, kHsThreads, smem, st>>>(ps, ps_stride, g, thr, first_template, tiles_per_template, total, keys);
     return cudaGetLastError();
 }
 
