@@ -179,8 +179,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     series, bank, g, name = workload(args)
+    from brp_b200 import sharding
     n_total = len(bank)
-    lo, hi = rank * n_total // world, (rank + 1) * n_total // world       # contiguous shards
+    lo, hi = sharding.shard_range(n_total, rank, world)       # contiguous shards
     shard = np.ascontiguousarray(bank[lo:hi])
 
     s = brp_b200.Search(g, fA=0.08, max_batch=args.batch, device=local)
@@ -235,18 +236,8 @@ def run_ours(args):
         s.run(shard, lo)                               # derives template constants on the host, H2D, enqueues all batches
         hits = s.collect()                             # D2H of the compacted per-bin maxima
         hit_bytes = hits.nbytes + 4
-        if dist is not None:
-            cap = torch.tensor([len(hits)], device="cuda")
-            dist.all_reduce(cap, op=dist.ReduceOp.MAX)
-            buf = torch.zeros((int(cap.item()) + 1, 4), dtype=torch.int32, device="cuda")
-            buf[0, 0] = len(hits)
-            if len(hits):
-                buf[1:len(hits) + 1] = torch.from_numpy(hits.view(np.int32).reshape(-1, 4)).cuda()
-            out = [torch.empty_like(buf) for _ in range(world)]
-            dist.all_gather(out, buf)                  # the single collective of the search: gather of per-GPU hit lists
-            if rank == 0:
-                parts = [o[1:int(o[0, 0].item()) + 1].cpu().numpy().view(brp_b200.HIT_DTYPE).reshape(-1) for o in out]
-                hits = np.concatenate(parts)
+        # the single exchange of the search: one all-gather of the per-GPU hit lists over NCCL
+        hits = sharding.gather_hits(hits, dist, torch.device("cuda", local))
         if rank == 0:
             return brp_b200.toplist_from_hits(hits, bank)
         return None
