@@ -41,6 +41,9 @@ constexpr int kThreads = 256;
 // ------------------------------------------------------------------ compile-time plan of one tile transform
 __host__ __device__ constexpr int cfg_radix(int L, int s)
 {
+    // two radix-32 stages for the production pass-2 length (one shared-memory exchange instead of two)
+    if (L == 1024) return s < 2 ? 32 : 0;
+    if (L == 512) return s == 0 ? 32 : (s == 1 ? 16 : 0);
     int rem = L;
     if (rem % 3 == 0) {
         if (s == 0) return 3;
@@ -85,12 +88,15 @@ __host__ __device__ constexpr int cfg_tw_size(int L) { return cfg_tw_offset(L, c
 // the digit-reversed reads of the untangle epilogue).
 template <int L, int ROWS, int PASS>
 struct Layout {
+    // the radix-32 plans (L = 1024: 32x32, L = 512: 32x16) pad every 32 (resp. 16) positions
+    static constexpr int C4 = (L == 1024 || (L == 512 && PASS == 1)) ? 0 : 1;
+    static constexpr int C5 = (L == 1024) ? 1 : 0;
     static constexpr int C8 = (PASS == 2 && (L == 2048 || L == 4096)) ? 1 : 0;
-    static constexpr int EXTRA = PASS == 2 ? (L == 2048 ? 4 : (L == 4096 || L == 16) ? 0 : 1)
-                                           : (ROWS == 4 ? (L % 3 == 0 ? 1 : 2) : ROWS == 2 ? (L == 4096 ? 8 : 4) : 1);
+    static constexpr int EXTRA = PASS == 2 ? (L == 2048 || L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
+                                           : (L == 1024 ? 2 : ROWS == 4 ? (L % 3 == 0 ? 1 : 2) : ROWS == 2 ? (L == 4096 ? 8 : 4) : 1);
     // permute the low four bits of the butterfly index in the first (global -> shared) stage of pass 1
-    static constexpr bool ROT0 = PASS == 1 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
-    __host__ __device__ static constexpr int phys(int pos) { return pos + (pos >> 4) + C8 * (pos >> 8); }
+    static constexpr bool ROT0 = PASS == 1 && L != 1024 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
+    __host__ __device__ static constexpr int phys(int pos) { return pos + C4 * (pos >> 4) + C5 * (pos >> 5) + C8 * (pos >> 8); }
     static constexpr int PITCH = phys(L) + EXTRA;
     static constexpr int BYTES = ROWS * PITCH * 8;
 };
@@ -124,7 +130,22 @@ __device__ __forceinline__ float2 mul_w16(float2 d)
     else return make_float2(fmaf(d.y, S1, -d.x * C1), -fmaf(d.x, S1, d.y * C1));
 }
 
-// in-register DFT of R = 2^a points, decimation in frequency; output q ends up in v[bitrev(q)]
+// multiply by exp(-2 pi i e / 32), e = 0..15
+template <int E>
+__device__ __forceinline__ float2 mul_w32(float2 d)
+{
+    if constexpr (E % 2 == 0) return mul_w16<E / 2>(d);
+    else {
+        // cos/sin of (2 pi E / 32) for odd E, from the two base angles pi/16 and 3 pi/16
+        constexpr float CA = 0.98078528040323044913f, SA = 0.19509032201612826785f;
+        constexpr float CB = 0.83146961230254523708f, SB = 0.55557023301960222474f;
+        constexpr float C = E == 1 ? CA : E == 3 ? CB : E == 5 ? SB : E == 7 ? SA : E == 9 ? -SA : E == 11 ? -SB : E == 13 ? -CB : -CA;
+        constexpr float S = E == 1 ? SA : E == 3 ? SB : E == 5 ? CB : E == 7 ? CA : E == 9 ? CA : E == 11 ? CB : E == 13 ? SB : SA;
+        return make_float2(fmaf(d.x, C, d.y * S), fmaf(d.y, C, -d.x * S)); // d * (C - i S)
+    }
+}
+
+// in-register DFT of R = 2^a points (R <= 32), decimation in frequency; output q ends up in v[bitrev(q)]
 template <int R>
 struct Dft {
     template <int J>
@@ -133,7 +154,7 @@ struct Dft {
         if constexpr (J < R / 2) {
             const float2 a = v[J], b = v[J + R / 2];
             v[J] = cadd(a, b);
-            v[J + R / 2] = mul_w16<J *(16 / R)>(csub(a, b));
+            v[J + R / 2] = mul_w32<J *(32 / R)>(csub(a, b));
             level<J + 1>(v);
         }
     }

@@ -11,6 +11,10 @@ THREADS = 256
 
 
 def radices(L):
+    if L == 1024:
+        return [32, 32]
+    if L == 512:
+        return [32, 16]
     out, rem = [], L
     if rem % 3 == 0:
         out.append(3); rem //= 3
