@@ -32,9 +32,9 @@ namespace {
 
 constexpr int kHsThreads = 256;
 constexpr int kHsPerThread = 4;                       // bins per thread, kHsThreads apart
-constexpr int kSpan = kHsThreads * kHsPerThread;      // bins per CTA
-// slice l holds at most l*kSpan/16 + 2 floats, rounded up to whole 16-byte units on both ends
-__host__ __device__ constexpr int slice_cap(int l) { return ((l * kSpan / 16 + 2 + 3 + 3) / 4) * 4; }
+constexpr int kSpan = kHsThreads * kHsPerThread;      // bins per tile; tiles start at multiples of kSpan
+// slice l of an aligned tile holds l*kSpan/16 + 1 floats, rounded up to whole 16-byte units
+__host__ __device__ constexpr int slice_cap(int l) { return ((l * kSpan / 16 + 1 + 3) / 4) * 4; }
 __host__ __device__ constexpr int slice_off(int l)
 {
     int o = 0;
@@ -45,18 +45,26 @@ constexpr int kSmemFloats = slice_off(17);
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ void offer(unsigned long long *slot, float power, uint32_t tkey)
+// rare path, kept out of line so that the hot loop stays small: offer every sum of bin i that beats its threshold
+__device__ __noinline__ void record_hits(uint32_t i, float s0, float s1, float s2, float s3, float s4, const BrpThresholds &thr,
+                                         uint32_t fu, uint32_t tkey, unsigned long long *__restrict__ keys)
 {
-    atomicMax(slot, ((unsigned long long)__float_as_uint(power) << 32) | tkey);
+    const float s[5] = {s0, s1, s2, s3, s4};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const uint32_t j = (i * (16u >> k) + 8u) >> 4; // fundamental bin of level k (hs_common.c:84,107,125,145)
+        if (s[k] > thr.t[k] && j < fu)
+            atomicMax(keys + (size_t)k * fu + j, ((unsigned long long)__float_as_uint(s[k]) << 32) | tkey);
+    }
 }
 
 // stage the sixteen harmonic slices of tile (bx, template b) into `dst` with bulk async copies (called by warp 0)
-__device__ __forceinline__ void issue_tile(const float *__restrict__ ps, size_t ps_stride, const BrpGeomDev &g, uint32_t tile,
-                                           uint32_t tiles_per_template, float *dst, uint32_t bar_addr)
+__device__ __forceinline__ void issue_tile(const float *__restrict__ ps, size_t ps_stride, const BrpGeomDev &g, uint32_t tile0,
+                                           uint32_t tile, uint32_t tiles_per_template, float *dst, uint32_t bar_addr)
 {
     const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
     const float *__restrict__ P = ps + (size_t)b * ps_stride;
-    const uint32_t i0 = g.w2 + bx * kSpan, i1 = min(i0 + kSpan, g.h) - 1;
+    const uint32_t i0 = (tile0 + bx) * kSpan, i1 = min(i0 + kSpan, g.h) - 1; // i0 is a multiple of kSpan
     const int l = (threadIdx.x & 31) + 1;
     uint32_t bytes = 0, first = 0;
     if (l <= 16) {
@@ -81,13 +89,12 @@ __device__ __forceinline__ void issue_tile(const float *__restrict__ ps, size_t 
 // bulk copies of the next tile run while the current one is summed.
 __global__ void __launch_bounds__(kHsThreads)
 harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomDev g, BrpThresholds thr,
-                        uint32_t first_template, uint32_t tiles_per_template, uint32_t total_tiles,
+                        uint32_t first_template, uint32_t tile0, uint32_t tiles_per_template, uint32_t total_tiles,
                         unsigned long long *__restrict__ keys)
 {
     extern __shared__ __align__(128) float sm[];
     __shared__ __align__(8) unsigned long long bar[2];
 
-    const uint32_t fu = g.fu;
     const uint32_t bar0 = smem_u32(&bar[0]);
     if (threadIdx.x == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
@@ -96,28 +103,25 @@ harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomD
     }
     __syncthreads();
     uint32_t tile = blockIdx.x;
-    if (tile < total_tiles && threadIdx.x < 32) issue_tile(ps, ps_stride, g, tile, tiles_per_template, sm, bar0);
+    if (tile < total_tiles && threadIdx.x < 32) issue_tile(ps, ps_stride, g, tile0, tile, tiles_per_template, sm, bar0);
+
+    // Tiles are aligned to kSpan, so bin i0 + t + 256 u of harmonic l sits at slice offset ((l t + 8) >> 4) + 16 l u:
+    // the first term is a per-thread constant for the whole kernel, the second an immediate.
+    uint32_t off[17];
+#pragma unroll
+    for (int l = 1; l <= 16; ++l) off[l] = slice_off(l) + (((uint32_t)l * threadIdx.x + 8u) >> 4);
 
     for (uint32_t n = 0; tile < total_tiles; tile += gridDim.x, ++n) {
         const uint32_t st = n & 1u;
         const uint32_t next = tile + gridDim.x;
         // the other stage was fully consumed before the __syncthreads that ended the previous iteration
         if (next < total_tiles && threadIdx.x < 32)
-            issue_tile(ps, ps_stride, g, next, tiles_per_template, sm + (st ^ 1u) * kSmemFloats, bar0 + 8 * (st ^ 1u));
+            issue_tile(ps, ps_stride, g, tile0, next, tiles_per_template, sm + (st ^ 1u) * kSmemFloats, bar0 + 8 * (st ^ 1u));
 
         const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
         const uint32_t tkey = 0xFFFFFFFFu - (first_template + b);
-        const uint32_t i0 = g.w2 + bx * kSpan;
-        const uint32_t i1 = min(i0 + kSpan, g.h) - 1;
-        // per-thread slice indices of its first bin (the only index arithmetic per tile)
-        const uint32_t i = i0 + threadIdx.x;
+        const uint32_t i = (tile0 + bx) * kSpan + threadIdx.x;
         const float *__restrict__ buf = sm + st * kSmemFloats;
-        uint32_t idx[17];
-#pragma unroll
-        for (int l = 1; l <= 16; ++l) {
-            const uint32_t first = (((uint32_t)l * i0 + 8u) >> 4) & ~3u;
-            idx[l] = slice_off(l) + ((((uint32_t)l * i + 8u) >> 4) - first);
-        }
         {   // wait for this stage's copies: use number n>>1 of the barrier -> parity (n>>1)&1
             const uint32_t parity = (n >> 1) & 1u, addr = bar0 + 8 * st;
             uint32_t done = 0;
@@ -131,24 +135,16 @@ harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomD
 #pragma unroll
         for (int u = 0; u < kHsPerThread; ++u) {
             const uint32_t iu = i + u * kHsThreads;
-            if (iu > i1) break;
-            // bins kHsThreads apart: slice index advances by exactly l*kHsThreads/16
-#define PH(l) buf[idx[l] + u * ((l) * kHsThreads / 16)]
+#define PH(l) buf[off[l] + u * ((l) * kHsThreads / 16)]
             const float s0 = PH(16);
             const float s1 = s0 + PH(8);
             const float s2 = s1 + (PH(12) + PH(4));
             const float s3 = s2 + (((PH(14) + PH(10)) + PH(6)) + PH(2));
             const float s4 = s3 + (((((((PH(15) + PH(13)) + PH(11)) + PH(9)) + PH(7)) + PH(5)) + PH(3)) + PH(1));
 #undef PH
-            if ((s0 > thr.t[0]) | (s1 > thr.t[1]) | (s2 > thr.t[2]) | (s3 > thr.t[3]) | (s4 > thr.t[4])) {
-                // rare path: fundamental bins j_k = (i*2^(4-k) + 8) >> 4 of this i
-                const uint32_t b1 = (8u * iu + 8u) >> 4, b2 = (4u * iu + 8u) >> 4, b3 = (2u * iu + 8u) >> 4, b4 = (iu + 8u) >> 4;
-                if (s0 > thr.t[0] && iu < fu) offer(keys + iu, s0, tkey);
-                if (s1 > thr.t[1] && b1 < fu) offer(keys + (size_t)fu + b1, s1, tkey);
-                if (s2 > thr.t[2] && b2 < fu) offer(keys + 2 * (size_t)fu + b2, s2, tkey);
-                if (s3 > thr.t[3] && b3 < fu) offer(keys + 3 * (size_t)fu + b3, s3, tkey);
-                if (s4 > thr.t[4] && b4 < fu) offer(keys + 4 * (size_t)fu + b4, s4, tkey);
-            }
+            const bool any = (s0 > thr.t[0]) | (s1 > thr.t[1]) | (s2 > thr.t[2]) | (s3 > thr.t[3]) | (s4 > thr.t[4]);
+            // bins outside [w2, H) only exist in the first and last tile of a template (their slots may hold stale data)
+            if (any && iu >= g.w2 && iu < g.h) record_hits(iu, s0, s1, s2, s3, s4, thr, g.fu, tkey, keys);
         }
         __syncthreads(); // everyone is done with stage `st` before it is refilled two iterations later
     }
@@ -197,10 +193,12 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
         if (e != cudaSuccess) return e;
         ctas_per_device[dev] = (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1); // one resident wave
     }
-    const uint32_t tiles_per_template = (g.h - g.w2 + kSpan - 1) / kSpan;
+    // aligned tiles covering [w2, H): tile index range [w2 / kSpan, ceil(H / kSpan))
+    const uint32_t tile0 = g.w2 / kSpan;
+    const uint32_t tiles_per_template = (g.h + kSpan - 1) / kSpan - tile0;
     const uint32_t total = tiles_per_template * (uint32_t)batch;
     const uint32_t grid = total < (uint32_t)ctas_per_device[dev] ? total : (uint32_t)ctas_per_device[dev];
-    harmonic_summing_kernel<<<grid, kHsThreads, smem, st>>>(ps, ps_stride, g, thr, first_template, tiles_per_template, total, keys);
+    harmonic_summing_kernel<<<grid, kHsThreads, smem, st>>>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total, keys);
     return cudaGetLastError();
 }
 

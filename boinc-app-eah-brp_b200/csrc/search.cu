@@ -31,9 +31,28 @@
         }                                                                                            \
     } while (0)
 
+// One lane = one stream with its own per-batch scratch.  Batches are dealt round-robin to the lanes so that kernels of
+// different batches overlap on the GPU: the stages are bound by different resources (resampler: issue slots, FFT
+// passes: L1/LSU wavefronts, harmonic sum: L2), so co-resident CTAs of different stages fill each other's idle units.
+struct BrpLane {
+    cudaStream_t st;
+    float *resamp;
+    uint32_t *nsteps;
+    float *mean;
+    double *partials;
+    uint32_t *counters;
+    float2 *work;
+    float *ps;
+    cudaEvent_t done;
+};
+#define BRP_MAX_LANES 4
+
 struct brp_search {
     int device;
     cudaStream_t stream;
+    BrpLane lane[BRP_MAX_LANES]; // lane[0] aliases the handle's own stream and scratch
+    int n_lanes;
+    cudaEvent_t ev_fork;
     brp_geometry g;
     BrpGeomDev gd;
     BrpThresholds thr;
@@ -89,6 +108,16 @@ int brp_search_destroy(brp_search *s)
     cudaFree(s->d_mean); cudaFree(s->d_partials); cudaFree(s->d_counters); cudaFree(s->d_work); cudaFree(s->d_ps);
     cudaFree(s->d_keys); cudaFree(s->d_hits); cudaFree(s->d_hit_counter); cudaFree(s->d_tap_series);
     cudaFree(s->d_tap_idx); cudaFree(s->d_tap_ps); cudaFree(s->d_tap_keys);
+    for (int l = 1; l < s->n_lanes; l++) {
+        BrpLane &ln = s->lane[l];
+        if (ln.st) cudaStreamSynchronize(ln.st);
+        cudaFree(ln.resamp); cudaFree(ln.nsteps); cudaFree(ln.mean); cudaFree(ln.partials); cudaFree(ln.counters);
+        cudaFree(ln.work); cudaFree(ln.ps);
+        if (ln.done) cudaEventDestroy(ln.done);
+        if (ln.st) cudaStreamDestroy(ln.st);
+    }
+    if (s->lane[0].done) cudaEventDestroy(s->lane[0].done);
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->ev_start) cudaEventDestroy(s->ev_start);
     if (s->ev_stop) cudaEventDestroy(s->ev_stop);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -148,6 +177,41 @@ int brp_search_create(brp_search **out, int device, const brp_geometry *g, float
     cudaMemsetAsync(s->d_counters, 0, sizeof(uint32_t) * B, s->stream);
     cudaMemsetAsync(s->d_keys, 0, sizeof(unsigned long long) * s->hit_cap, s->stream);
     cudaMemsetAsync(s->d_ps, 0, sizeof(float) * s->ps_stride * B, s->stream);
+    // lanes: BRP_STREAMS (default 1) streams with private scratch; lane 0 is the handle's own
+    {
+        const char *env = getenv("BRP_STREAMS");
+        int want = env ? atoi(env) : 1; // measured on B200: 2-4 lanes are ~10 % SLOWER than one (L2 thrash), so off by default
+        if (want < 1) want = 1;
+        if (want > BRP_MAX_LANES) want = BRP_MAX_LANES;
+        s->n_lanes = 1;
+        BrpLane &l0 = s->lane[0];
+        l0.st = s->stream; l0.resamp = s->d_resamp; l0.nsteps = s->d_nsteps; l0.mean = s->d_mean; l0.partials = s->d_partials;
+        l0.counters = s->d_counters; l0.work = s->d_work; l0.ps = s->d_ps;
+        bool ok = cudaEventCreateWithFlags(&l0.done, cudaEventDisableTiming) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int l = 1; ok && l < want; l++) {
+            BrpLane &ln = s->lane[l];
+            ok = cudaMalloc((void **)&ln.resamp, sizeof(float) * s->rs_stride * B) == cudaSuccess &&
+                 cudaMalloc((void **)&ln.nsteps, sizeof(uint32_t) * B) == cudaSuccess &&
+                 cudaMalloc((void **)&ln.mean, sizeof(float) * B) == cudaSuccess &&
+                 cudaMalloc((void **)&ln.partials, sizeof(double) * s->nblk * B) == cudaSuccess &&
+                 cudaMalloc((void **)&ln.counters, sizeof(uint32_t) * B) == cudaSuccess &&
+                 cudaMalloc((void **)&ln.work, sizeof(float2) * (size_t)s->plan.m * B) == cudaSuccess &&
+                 cudaMalloc((void **)&ln.ps, sizeof(float) * s->ps_stride * B) == cudaSuccess &&
+                 cudaStreamCreateWithFlags(&ln.st, cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&ln.done, cudaEventDisableTiming) == cudaSuccess;
+            s->n_lanes = l + 1; // so that destroy releases a partially built lane too
+            if (ok) {
+                cudaMemsetAsync(ln.counters, 0, sizeof(uint32_t) * B, s->stream);
+                cudaMemsetAsync(ln.ps, 0, sizeof(float) * s->ps_stride * B, s->stream);
+            }
+        }
+        if (!ok) {
+            fprintf(stderr, "[brp_b200] could not set up %d lanes\n", want);
+            brp_search_destroy(s);
+            return RADPUL_CUDA_MEM_ALLOC_DEVICE;
+        }
+    }
     CU_TRY(cudaStreamSynchronize(s->stream), RADPUL_CUDA_KERNEL_INVOKE);
     *out = s;
     return 0;
@@ -209,22 +273,22 @@ static int upload_templates(brp_search *s, const double *bank, uint32_t n)
     return 0;
 }
 
-static int run_batch(brp_search *s, uint32_t first, uint32_t nb, uint32_t first_global, unsigned long long *keys,
-                     cudaEvent_t *ev /* optional 5 events */)
+static int run_batch(brp_search *s, const BrpLane &ln, uint32_t first, uint32_t nb, uint32_t first_global,
+                     unsigned long long *keys, cudaEvent_t *ev /* optional 5 events */)
 {
     const float norm = 1.0f / (float)s->g.nsamples; /* demod_binary.c:1255 */
-    if (ev) cudaEventRecord(ev[0], s->stream);
-    CU_TRY(brp_launch_resample(s->d_series, s->d_tmpl + first, (int)nb, s->gd, s->d_resamp, s->rs_stride, NULL, s->d_nsteps,
-                               s->d_mean, s->d_partials, s->d_counters, false, s->stream),
+    if (ev) cudaEventRecord(ev[0], ln.st);
+    CU_TRY(brp_launch_resample(s->d_series, s->d_tmpl + first, (int)nb, s->gd, ln.resamp, s->rs_stride, NULL, ln.nsteps, ln.mean,
+                               ln.partials, ln.counters, false, ln.st),
            RADPUL_CUDA_KERNEL_INVOKE);
-    if (ev) cudaEventRecord(ev[1], s->stream);
-    CU_TRY(brp_launch_fft_power(s->plan, s->d_resamp, s->rs_stride, s->d_nsteps, s->d_mean, s->d_work, s->d_ps, s->ps_stride,
-                                s->g.harmonic_idx_hi, norm, (int)nb, s->stream, ev ? ev[2] : NULL),
+    if (ev) cudaEventRecord(ev[1], ln.st);
+    CU_TRY(brp_launch_fft_power(s->plan, ln.resamp, s->rs_stride, ln.nsteps, ln.mean, ln.work, ln.ps, s->ps_stride,
+                                s->g.harmonic_idx_hi, norm, (int)nb, ln.st, ev ? ev[2] : NULL),
            RADPUL_CUDA_FFT_EXEC);
-    if (ev) cudaEventRecord(ev[3], s->stream);
-    CU_TRY(brp_launch_harmonic_summing(s->d_ps, s->ps_stride, (int)nb, s->gd, s->thr, first_global + first, keys, s->stream),
+    if (ev) cudaEventRecord(ev[3], ln.st);
+    CU_TRY(brp_launch_harmonic_summing(ln.ps, s->ps_stride, (int)nb, s->gd, s->thr, first_global + first, keys, ln.st),
            RADPUL_CUDA_KERNEL_INVOKE);
-    if (ev) cudaEventRecord(ev[4], s->stream);
+    if (ev) cudaEventRecord(ev[4], ln.st);
     s->launches += 4;
     return 0;
 }
@@ -236,10 +300,19 @@ int brp_search_run(brp_search *s, const double *bank, uint32_t n_templates, uint
     int rc = upload_templates(s, bank, n_templates);
     if (rc) return rc;
     cudaEventRecord(s->ev_start, s->stream);
-    for (uint32_t first = 0; first < n_templates; first += s->max_batch) {
+    // fork: the other lanes start after everything already queued on the handle's stream (series, templates, reset)
+    cudaEventRecord(s->ev_fork, s->stream);
+    for (int l = 1; l < s->n_lanes; l++) cudaStreamWaitEvent(s->lane[l].st, s->ev_fork, 0);
+    uint32_t k = 0;
+    for (uint32_t first = 0; first < n_templates; first += s->max_batch, k++) {
         const uint32_t nb = n_templates - first < s->max_batch ? n_templates - first : s->max_batch;
-        rc = run_batch(s, first, nb, first_global_index, s->d_keys, NULL);
+        rc = run_batch(s, s->lane[k % s->n_lanes], first, nb, first_global_index, s->d_keys, NULL);
         if (rc) return rc;
+    }
+    // join: the handle's stream continues only after every lane has drained
+    for (int l = 1; l < s->n_lanes; l++) {
+        cudaEventRecord(s->lane[l].done, s->lane[l].st);
+        cudaStreamWaitEvent(s->stream, s->lane[l].done, 0);
     }
     cudaEventRecord(s->ev_stop, s->stream);
     s->timed = true;
@@ -303,9 +376,9 @@ int brp_search_profile_batch(brp_search *s, const double *bank, uint32_t batch, 
     cudaEvent_t ev[5];
     for (int i = 0; i < 5; i++) CU_TRY(cudaEventCreate(&ev[i]), RADPUL_CUDA_DEVICE_SET);
     double acc[4] = {0, 0, 0, 0};
-    rc = run_batch(s, 0, batch, 0, s->d_tap_keys, NULL); // warm-up
+    rc = run_batch(s, s->lane[0], 0, batch, 0, s->d_tap_keys, NULL); // warm-up
     for (uint32_t r = 0; r < repeats && !rc; r++) {
-        rc = run_batch(s, 0, batch, 0, s->d_tap_keys, ev);
+        rc = run_batch(s, s->lane[0], 0, batch, 0, s->d_tap_keys, ev);
         if (rc) break;
         if (cudaStreamSynchronize(s->stream) != cudaSuccess) { rc = RADPUL_CUDA_KERNEL_INVOKE; break; }
         for (int i = 0; i < 4; i++) {
