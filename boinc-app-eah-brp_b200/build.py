@@ -22,6 +22,9 @@ NVCC_FLAGS = [
 ]
 
 
+PER_SOURCE_FLAGS: dict[str, list[str]] = {}
+
+
 def _stale(out: Path, deps: list[Path]) -> bool:
     if not out.exists():
         return True
@@ -39,7 +42,7 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
         obj = objdir / (src.rsplit(".", 1)[0] + ".o")
         objs.append(obj)
         if force or _stale(obj, [CSRC / src] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu", "-c", str(CSRC / src), "-o", str(obj)]
+            cmd = [nvcc] + NVCC_FLAGS + PER_SOURCE_FLAGS.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu", "-c", str(CSRC / src), "-o", str(obj)]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for src, p in procs:

@@ -101,4 +101,84 @@ __device__ __forceinline__ int brp_round_index_exact(float f)
     return v < 0 ? 0 : v;
 }
 
+// ---- two samples per instruction: Blackwell packed FP32x2 arithmetic (FADD2 / FMUL2 / FFMA2, every rounding mode).
+// Each lane of a packed operation rounds exactly like the scalar intrinsic above, so the pair version is bit-identical
+// to two scalar evaluations; a - b is written as fma(b, -1, a), which is one exact product and one rounding.
+// Only valid while |x / 2pi| < 2^22 for both lanes (the caller checks the template's largest argument once).
+// The CUDA builtins __fmul2_rn/__fadd2_rn are NOT safe here: nvcc contracts a packed multiply followed by a packed add
+// into FFMA2 even with -fmad=false (seen in SASS; ~4 % of the resampling indices changed).  PTX instructions that carry
+// an explicit rounding modifier are never contracted by ptxas, so the packed operations are spelled in PTX.
+#define BRP_PK2(name, op)                                                                                              \
+    __device__ __forceinline__ float2 name(float2 a, float2 b)                                                         \
+    {                                                                                                                  \
+        float2 r;                                                                                                      \
+        asm("{\n .reg .b64 ra, rb, rc;\n mov.b64 ra, {%2, %3};\n mov.b64 rb, {%4, %5};\n " op " rc, ra, rb;\n"         \
+            " mov.b64 {%0, %1}, rc;\n}"                                                                                \
+            : "=f"(r.x), "=f"(r.y)                                                                                     \
+            : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));                                                                 \
+        return r;                                                                                                      \
+    }
+// ptxas nevertheless contracts "mul.rn.f32x2 ; add.rn.f32x2" into FFMA2 (CUDA 12.9, also with -fmad=false), which the
+// scalar forms never do.  Hence brp_add2_of_product(): an addition whose operand is a fresh packed product is done with
+// two scalar __fadd_rn, which are protected; everything else stays packed.  The index arrays of
+// tests/test_gpu_resample.py are the check: bit-exact against the oracle.
+BRP_PK2(brp_mul2, "mul.rn.f32x2")
+BRP_PK2(brp_add2, "add.rn.f32x2")
+BRP_PK2(brp_add2_rd, "add.rm.f32x2")
+#undef BRP_PK2
+__device__ __forceinline__ float2 brp_fma2(float2 a, float2 b, float2 c)
+{
+    float2 r;
+    asm("{\n .reg .b64 ra, rb, rc, rd;\n mov.b64 ra, {%2, %3};\n mov.b64 rb, {%4, %5};\n mov.b64 rc, {%6, %7};\n"
+        " fma.rn.f32x2 rd, ra, rb, rc;\n mov.b64 {%0, %1}, rd;\n}"
+        : "=f"(r.x), "=f"(r.y)
+        : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return r;
+}
+__device__ __forceinline__ float2 brp_add2_of_product(float2 prod, float2 c)
+{
+    return make_float2(__fadd_rn(prod.x, c.x), __fadd_rn(prod.y, c.y));
+}
+__device__ __forceinline__ float2 brp_pair(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float2 brp_sub2(float2 a, float2 b) { return brp_fma2(b, make_float2(-1.0f, -1.0f), a); }
+
+template <typename Table>
+__device__ __forceinline__ float2 brp_sin_lut2(float2 x, const Table &tab)
+{
+    const float2 y = brp_mul2(brp_pair(BRP_TWO_PI_INV), x);
+    const float2 r = brp_add2(brp_add2(y, brp_pair(12582912.0f)), brp_pair(-12582912.0f));
+    const float2 fr = brp_sub2(y, r);
+    const float2 wrap = make_float2(fr.x < 0.0f ? 1.0f : 0.0f, fr.y < 0.0f ? 1.0f : 0.0f); // fr + 0 is exact
+    const float2 xt = brp_add2(fr, wrap);
+    const float2 z = brp_fma2(xt, brp_pair(64.0f), brp_pair(0.5f));
+    const float2 zf = brp_add2_rd(z, brp_pair(8388608.0f));
+    const int i0 = __float_as_int(zf.x) & 0xFF, i1 = __float_as_int(zf.y) & 0xFF;
+    const float2 i0f = brp_add2(zf, brp_pair(-8388608.0f));
+    const float2 d = brp_mul2(brp_pair(BRP_TWO_PI), brp_fma2(i0f, brp_pair(-0.015625f), xt));
+    const float2 d2 = brp_mul2(d, brp_mul2(brp_pair(0.5f), d));
+    const float2 sc0 = tab[i0], sc1 = tab[i1];
+    const float2 ts = make_float2(sc0.x, sc1.x), tc = make_float2(sc0.y, sc1.y);
+    return brp_sub2(brp_add2_of_product(brp_mul2(d, tc), ts), brp_mul2(d2, ts));
+}
+
+template <typename Table>
+__device__ __forceinline__ float2 brp_del_t2(float2 i_f, float tau, float Omega, float Psi0, float S0, float dt,
+                                             float step_inv, const Table &tab)
+{
+    const float2 t = brp_mul2(i_f, brp_pair(dt));
+    const float2 s = brp_sin_lut2(brp_add2_of_product(brp_mul2(brp_pair(Omega), t), brp_pair(Psi0)), tab);
+    return brp_sub2(brp_mul2(brp_mul2(brp_pair(tau), s), brp_pair(step_inv)), brp_pair(S0));
+}
+
+// pair version of brp_round_index_fast
+__device__ __forceinline__ int2 brp_round_index_fast2(float2 f)
+{
+    const float2 fp = make_float2(fmaxf(f.x, 0.0f), fmaxf(f.y, 0.0f));
+    const float2 s = brp_add2_rd(fp, brp_pair(8388608.0f));
+    const float2 fl = brp_add2(s, brp_pair(-8388608.0f));
+    const float2 frac = brp_sub2(fp, fl);
+    return make_int2((__float_as_int(s.x) & 0x7FFFFF) + (frac.x >= 0.5f ? 1 : 0),
+                     (__float_as_int(s.y) & 0x7FFFFF) + (frac.y >= 0.5f ? 1 : 0));
+}
+
 #endif

@@ -94,6 +94,8 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
     // ---- gather: out[i] = series[(int)(i - del_t[i] + 0.5)] for i < n_steps  (demod_binary_resamp_cpu.c:113-121)
     float *const orow = out + (size_t)b * out_stride;
     double acc = 0.0;
+    // the packed path needs |Omega*t + Psi0| / 2pi < 2^22 for every sample: true for any physical template
+    const bool packed_ok = (fabsf(tp.Omega) * ((float)nu * g.dt) + fabsf(tp.Psi0)) * BRP_TWO_PI_INV < 4.0e6f;
 #pragma unroll
     for (int it = 0; it < BRP_RESAMP_SAMPLES_PER_BLOCK / (4 * BRP_RESAMP_THREADS); ++it) {
         const uint32_t i0 = block_lo + (uint32_t)it * (4 * BRP_RESAMP_THREADS) + 4u * threadIdx.x;
@@ -101,15 +103,27 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
         float v[4];
         int id[4];
         const float base = (float)i0;
+        if (FAST && packed_ok) {
+            // two samples per instruction (FADD2/FMUL2/FFMA2), bit-identical to the scalar path
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const float fi = __fadd_rn(base, (float)e); // exact: integers below 2^24
-            const float dl = brp_del_t(fi, tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab);
-            int k = round_index<FAST>(__fsub_rn(fi, dl));
-            k = min(k, (int)nu - 1); // the reference would read past the array here; keep the access in bounds
-            id[e] = k;
-            v[e] = __ldg(series + k);
+            for (int e = 0; e < 4; e += 2) {
+                const float2 fi = brp_add2(brp_pair(base), make_float2((float)e, (float)(e + 1)));
+                const float2 dl = brp_del_t2(fi, tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab);
+                const int2 k = brp_round_index_fast2(brp_sub2(fi, dl));
+                id[e] = min(k.x, (int)nu - 1);
+                id[e + 1] = min(k.y, (int)nu - 1);
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float fi = __fadd_rn(base, (float)e); // exact: integers below 2^24
+                const float dl = brp_del_t(fi, tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab);
+                const int k = round_index<FAST>(__fsub_rn(fi, dl));
+                id[e] = min(k, (int)nu - 1); // the reference would read past the array here; keep the access in bounds
+            }
         }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] = __ldg(series + id[e]);
         if (i0 + 3 < n_steps) {
             *reinterpret_cast<float4 *>(orow + i0) = make_float4(v[0], v[1], v[2], v[3]);
             acc += (double)((v[0] + v[1]) + (v[2] + v[3]));
