@@ -271,8 +271,15 @@ def run_ours(args):
         for v in stages.values():
             v["frac"] = v["GBps"] / peak
         dom = max(stages, key=lambda k: stages[k]["ms_per_batch"])
+        # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture (same batch size only)
+        traffic = None
+        tpath = ROOT / "profiles" / "r1_traffic.json"
+        if tpath.exists() and args.log2n == 22 and args.padding == 1.0:
+            t = json.loads(tpath.read_text())
+            if t.get("batch") == nb:
+                traffic = t["dram_bytes_per_launch"].get(dom)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["GBps"], "peak": peak, "peak_source": peak_src,
-                    "unit": "GB/s", "frac": stages[dom]["GBps"] / peak, "traffic": None,
+                    "unit": "GB/s", "frac": stages[dom]["GBps"] / peak, "traffic": traffic,
                     "algorithmic_bytes_per_template": alg, "templates_per_launch": nb, "stages": stages,
                     "whole_loop": {"GBps": alg["total"] * value / 1e9, "frac": alg["total"] * value / 1e9 / peak}}
         cpu = None
