@@ -36,7 +36,10 @@
 
 namespace {
 
-constexpr int kThreads = 256;
+#ifndef BRP_BIG_TILE_L
+#define BRP_BIG_TILE_L 0 // tile length that gets a 16384-element tile (8 rows, 512 threads, one CTA per SM); 0 = none.
+// Measured with 2048 on B200: 64-byte global runs but only one CTA per SM -> pass 1 takes 178 us instead of 164 us.
+#endif
 
 // ------------------------------------------------------------------ compile-time plan of one tile transform
 __host__ __device__ constexpr int cfg_radix(int L, int s)
@@ -92,7 +95,7 @@ struct Layout {
     static constexpr int C4 = (L == 1024 || (L == 512 && PASS == 1)) ? 0 : 1;
     static constexpr int C5 = (L == 1024) ? 1 : 0;
     static constexpr int C8 = (PASS == 2 && (L == 2048 || L == 4096)) ? 1 : 0;
-    static constexpr int EXTRA = PASS == 2 ? (L == 2048 || L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
+    static constexpr int EXTRA = PASS == 2 ? (L == 2048 ? (ROWS == 8 ? 2 : 4) : L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
                                            : (L == 1024 ? 2 : ROWS == 4 ? (L % 3 == 0 ? 1 : 2) : ROWS == 2 ? (L == 4096 ? 8 : 4) : 1);
     // permute the low four bits of the butterfly index in the first (global -> shared) stage of pass 1
     static constexpr bool ROT0 = PASS == 1 && L != 1024 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
@@ -102,9 +105,11 @@ struct Layout {
 };
 __host__ __device__ constexpr int cfg_rows(int L)
 {
-    const int tile = (L % 3 == 0) ? 12288 : 8192;
+    const int tile = (L % 3 == 0) ? 12288 : (L == BRP_BIG_TILE_L ? 16384 : 8192);
     return tile / L < 2 ? 2 : tile / L;
 }
+
+__host__ __device__ constexpr int cfg_threads(int L) { return cfg_rows(L) * L >= 16384 ? 512 : 256; }
 
 // ------------------------------------------------------------------ complex helpers
 // Blackwell packed FP32x2 arithmetic (FADD2 / FFMA2): one instruction per complex add or subtract
@@ -234,10 +239,11 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
     constexpr int ITEMS = ROWS * BF;
     constexpr bool LAST = (STAGE == cfg_stages(L) - 1);
     constexpr int TWO = cfg_tw_offset(L, STAGE);
-    static_assert(ITEMS % kThreads == 0, "tile must be a whole number of butterflies per thread");
+    constexpr int NT = cfg_threads(L);
+    static_assert(ITEMS % NT == 0, "tile must be a whole number of butterflies per thread");
 #pragma unroll
-    for (int it = 0; it < ITEMS / kThreads; ++it) {
-        const int item = threadIdx.x + it * kThreads;
+    for (int it = 0; it < ITEMS / NT; ++it) {
+        const int item = threadIdx.x + it * NT;
         int row, bf;
         if (MAP == MAP_ROW_FAST) {
             row = item % ROWS;
@@ -385,7 +391,7 @@ struct Pass1Store {
 };
 
 template <int L, int ROWS>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(cfg_threads(L), cfg_threads(L) == 512 ? 1 : 2)
 fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t *__restrict__ n_steps_arr,
                  const float *__restrict__ mean_arr, float2 *__restrict__ work, uint32_t m1, uint32_t m,
                  const float2 *__restrict__ tw, const float2 *__restrict__ tb)
@@ -427,7 +433,7 @@ struct Pass2Load {
 };
 
 template <int L, int ROWS>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(cfg_threads(L), cfg_threads(L) == 512 ? 1 : 2)
 fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
                  uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
                  const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
@@ -451,7 +457,7 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
     //   E = (Z[k] + conj Z[M-k])/2,  O = (Z[k] - conj Z[M-k])/(2i)
     //   X[k] = E + W_N^k O,  X[M-k] = conj(E - W_N^k O)            (N = 2M)
 #pragma unroll 4
-    for (int item = threadIdx.x; item < T2 * (int)M1; item += kThreads) {
+    for (int item = threadIdx.x; item < T2 * (int)M1; item += cfg_threads(L)) {
         const int r = item % T2;
         const uint32_t k1 = item / T2;
         const uint32_t k2 = a + r;
@@ -486,7 +492,7 @@ typedef void (*pass2_fn)(const float2 *, float *, size_t, uint32_t, uint32_t, ui
                          const float2 *);
 
 struct TileInfo {
-    int L, rows, smem1, smem2, tw_size, last_radix;
+    int L, rows, threads, smem1, smem2, tw_size, last_radix;
     pass1_fn p1;
     pass2_fn p2;
 };
@@ -498,6 +504,7 @@ TileInfo make_info()
     TileInfo t;
     t.L = L;
     t.rows = ROWS;
+    t.threads = cfg_threads(L);
     t.smem1 = Layout<L, ROWS, 1>::BYTES;
     t.smem2 = Layout<L, ROWS, 2>::BYTES;
     t.tw_size = cfg_tw_size(L);
@@ -631,13 +638,13 @@ cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
-    t1->p1<<<g1, kThreads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
+    t1->p1<<<g1, t1->threads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (mid_event) cudaEventRecord(mid_event, st);
     const int T2 = t2->rows / 2;
     const dim3 g2((p.m2 / 2 + 1 + T2 - 1) / T2, batch); // rows k2 = 0 .. m2/2
-    t2->p2<<<g2, kThreads, t2->smem2, st>>>(work, ps, ps_stride, ps_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
+    t2->p2<<<g2, t2->threads, t2->smem2, st>>>(work, ps, ps_stride, ps_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
                                            p.tw_untangle_b);
     return cudaGetLastError();
 }
