@@ -90,7 +90,7 @@ EXPORTED_SYMBOLS = [
     "brp_search_set_series_device", "brp_search_reset", "brp_search_run", "brp_search_sync", "brp_search_collect",
     "brp_search_last_run_ms", "brp_search_stream", "brp_search_kernel_launches", "brp_search_profile_batch",
     "brp_stage_resample", "brp_stage_spectrum", "brp_stage_spectrum_of", "brp_stage_harmonic_summing",
-    "brp_stage_sin_lut", "brp_stage_round_index", "brp_resample_noalloc",
+    "brp_stage_sin_lut", "brp_stage_round_index", "brp_resample_noalloc", "brp_whiten_series",
 ]
 
 
@@ -151,6 +151,8 @@ lib.brp_stage_round_index.argtypes = [C.c_int, _f32, _i32, C.c_uint32]
 
 lib.brp_resample_noalloc.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(Template), C.c_float, C.c_float, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p]
+
+lib.brp_whiten_series.argtypes = [C.c_int, _f32, C.c_uint32, C.c_float, C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]
 
 lib.initialize_cuda.argtypes = [C.c_int, C.POINTER(C.c_int)]
 lib.set_up_resampling.argtypes = [DIfloatPtr, C.POINTER(DIfloatPtr), C.POINTER(ResampParams), C.c_void_p, C.c_void_p]
@@ -381,6 +383,14 @@ def resample_noalloc(d_series: int, g: Geometry, t: Template, d_out: int, d_n_st
     ``tensor.data_ptr()`` of buffers the caller owns); nothing is allocated by the call, the work is only enqueued."""
     _check(lib.brp_resample_noalloc(d_series, g.nsamples_unpadded, g.nsamples, C.byref(t), g.dt, g.step_inv, d_out, d_n_steps,
                                     d_mean, stream), "brp_resample_noalloc")
+
+
+def whiten_series(series: np.ndarray, padding: float, window: int = 1000, device: int = 0):
+    """``brp_whiten_series``: returns (whitened copy, device milliseconds)."""
+    out = np.ascontiguousarray(series, np.float32).copy()
+    ms = C.c_float(0)
+    _check(lib.brp_whiten_series(device, out, out.size, padding, window, 0, C.byref(ms)), "brp_whiten_series")
+    return out, ms.value
 
 
 def search_bank(series: np.ndarray, g: Geometry, bank: np.ndarray, fA: float = 0.08, max_batch: int = 16, device: int = 0):

@@ -12,7 +12,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "libbrp_b200.so"
-SOURCES = ["resamp.cu", "fft.cu", "hs.cu", "search.cu", "legacy.cu", "noalloc.cu", "host.cpp"]
+SOURCES = ["resamp.cu", "fft.cu", "hs.cu", "search.cu", "legacy.cu", "noalloc.cu", "whiten.cu", "host.cpp"]
 HEADERS = ["brp_internal.h", "brp_device.cuh", "../../include/brp_b200.h"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

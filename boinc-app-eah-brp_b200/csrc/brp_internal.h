@@ -62,6 +62,11 @@ cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in
                                  const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
                                  float norm, int batch, cudaStream_t st, cudaEvent_t mid_event);
 
+cudaError_t brp_launch_fft_spectrum(const BrpFftPlan &p, const float *in, const uint32_t *n_steps, const float *mean,
+                                    float2 *work, float2 *spectrum, uint32_t count, cudaStream_t st);
+cudaError_t brp_launch_fft_conj(const BrpFftPlan &p, const float2 *in, const uint32_t *n_steps_full, const float *mean,
+                                float2 *work, float *out, uint32_t pairs, float scale, cudaStream_t st);
+
 // ---------------- harmonic summing + per-bin toplist (hs.cu) ----------------
 struct BrpThresholds {
     float t[5];

@@ -432,7 +432,13 @@ struct Pass2Load {
     __device__ __forceinline__ float2 get(const float2 *c, int off) const { return c ? c[off] : make_float2(0.f, 0.f); }
 };
 
-template <int L, int ROWS>
+// MODE 0: power spectrum norm*|X|^2 of the real-input transform (the per-template hot path)
+// MODE 1: the real-input transform itself, X[0..M] as float2 (whitening pre-step, forward direction)
+// MODE 2: the plain complex transform Z[0..M) written as scale*conj(Z) pairs, i.e. out[2k] = s Re Z[k], out[2k+1] = -s Im Z[k]
+//         (backward real transform = conj(FFT(conj(.))), whitening pre-step; `ps_count` = number of float2 pairs wanted)
+enum { PASS2_POWER = 0, PASS2_SPECTRUM = 1, PASS2_CONJ = 2 };
+
+template <int L, int ROWS, int MODE>
 __global__ void __launch_bounds__(cfg_threads(L), cfg_threads(L) == 512 ? 1 : 2)
 fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
                  uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
@@ -452,6 +458,23 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
     __syncthreads();
     tile_middle<L, ROWS, 2, 1, NS>(tw, sm);
 
+    if constexpr (MODE == PASS2_CONJ) {
+        // every row of the tile is an output row here; rows are owned once: k2 <= m2/2 as "A" rows, the rest as mirrors
+        float2 *out = reinterpret_cast<float2 *>(ps) + (size_t)b * ps_stride;
+        for (int item = threadIdx.x; item < ROWS * (int)M1; item += cfg_threads(L)) {
+            const int r = item % ROWS;
+            const uint32_t k1 = item / ROWS;
+            const uint32_t f = a + (uint32_t)(r < T2 ? r : r - T2);
+            if (2 * f > m2) continue;
+            if (r >= T2 && (f == 0 || 2 * f == m2)) continue; // self-mirrored rows already written as "A" rows
+            const uint32_t k2 = r < T2 ? f : m2 - f;
+            const uint32_t k = k2 + m2 * k1;
+            if (k >= ps_count) continue;
+            const float2 z = *io.begin(r, pos_of_freq<L>((int)k1));
+            out[k] = make_float2(norm * z.x, -norm * z.y);
+        }
+        return;
+    }
     // ---- untangle + power.  Pair (k, M-k): Z[k] in row r at k1, Z[M-k] in row r+T2 at k1' = M1-1-k1
     // (k1' = (M1-k1) mod M1 on the self-mirrored row k2 = 0).
     //   E = (Z[k] + conj Z[M-k])/2,  O = (Z[k] - conj Z[M-k])/(2i)
@@ -480,8 +503,14 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
         const uint32_t k = k2 + m2 * k1;
         const uint32_t km = m - k;
         const float2 xp = cadd(e, wo), xm = csub(e, wo);
-        if (k < ps_count) P[k] = (k == 0) ? 0.0f : norm * fmaf(xp.x, xp.x, xp.y * xp.y);
-        if (km < ps_count && km != k) P[km] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+        if constexpr (MODE == PASS2_SPECTRUM) {
+            float2 *X = reinterpret_cast<float2 *>(ps) + (size_t)b * ps_stride;
+            if (k < ps_count) X[k] = xp;
+            if (km < ps_count && km != k) X[km] = make_float2(xm.x, -xm.y);
+        } else {
+            if (k < ps_count) P[k] = (k == 0) ? 0.0f : norm * fmaf(xp.x, xp.x, xp.y * xp.y);
+            if (km < ps_count && km != k) P[km] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+        }
     }
 }
 
@@ -494,7 +523,7 @@ typedef void (*pass2_fn)(const float2 *, float *, size_t, uint32_t, uint32_t, ui
 struct TileInfo {
     int L, rows, threads, smem1, smem2, tw_size, last_radix;
     pass1_fn p1;
-    pass2_fn p2;
+    pass2_fn p2, p2_spectrum, p2_conj;
 };
 
 template <int L>
@@ -510,7 +539,9 @@ TileInfo make_info()
     t.tw_size = cfg_tw_size(L);
     t.last_radix = cfg_radix(L, cfg_stages(L) - 1);
     t.p1 = fft_pass1_kernel<L, ROWS>;
-    t.p2 = fft_pass2_kernel<L, ROWS>;
+    t.p2 = fft_pass2_kernel<L, ROWS, PASS2_POWER>;
+    t.p2_spectrum = fft_pass2_kernel<L, ROWS, PASS2_SPECTRUM>;
+    t.p2_conj = fft_pass2_kernel<L, ROWS, PASS2_CONJ>;
     return t;
 }
 
@@ -614,7 +645,9 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
     // (measured: forcing the maximum shared-memory carve-out slows both passes by 15-35 %: the twiddle tables and the
     //  short global runs live off the L1 that is left over, so the driver's default split is kept)
     if (cudaFuncSetAttribute((const void *)t1->p1, cudaFuncAttributeMaxDynamicSharedMemorySize, t1->smem1) != cudaSuccess ||
-        cudaFuncSetAttribute((const void *)t2->p2, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem2) != cudaSuccess) {
+        cudaFuncSetAttribute((const void *)t2->p2, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem2) != cudaSuccess ||
+        cudaFuncSetAttribute((const void *)t2->p2_spectrum, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem2) != cudaSuccess ||
+        cudaFuncSetAttribute((const void *)t2->p2_conj, cudaFuncAttributeMaxDynamicSharedMemorySize, t2->smem2) != cudaSuccess) {
         brp_fft_plan_destroy(p);
         return RADPUL_CUDA_FFT_PLAN;
     }
@@ -632,9 +665,9 @@ void brp_fft_plan_destroy(BrpFftPlan *p)
     memset(p, 0, sizeof(*p));
 }
 
-cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in_stride, const uint32_t *n_steps,
-                                 const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
-                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event)
+static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, size_t in_stride, const uint32_t *n_steps,
+                              const float *mean, float2 *work, float *out, size_t out_stride, uint32_t out_count, float norm,
+                              int batch, cudaStream_t st, cudaEvent_t mid_event)
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
@@ -644,7 +677,29 @@ cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in
     if (mid_event) cudaEventRecord(mid_event, st);
     const int T2 = t2->rows / 2;
     const dim3 g2((p.m2 / 2 + 1 + T2 - 1) / T2, batch); // rows k2 = 0 .. m2/2
-    t2->p2<<<g2, t2->threads, t2->smem2, st>>>(work, ps, ps_stride, ps_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
-                                           p.tw_untangle_b);
+    const pass2_fn k2 = mode == PASS2_POWER ? t2->p2 : (mode == PASS2_SPECTRUM ? t2->p2_spectrum : t2->p2_conj);
+    k2<<<g2, t2->threads, t2->smem2, st>>>(work, out, out_stride, out_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
+                                         p.tw_untangle_b);
     return cudaGetLastError();
+}
+
+cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in_stride, const uint32_t *n_steps,
+                                 const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
+                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event)
+{
+    return launch_fft(p, PASS2_POWER, in, in_stride, n_steps, mean, work, ps, ps_stride, ps_count, norm, batch, st, mid_event);
+}
+
+// X[0..count) of the real-input transform of `in` (n reals; samples >= *n_steps read as *mean), count <= n/2 + 1
+cudaError_t brp_launch_fft_spectrum(const BrpFftPlan &p, const float *in, const uint32_t *n_steps, const float *mean,
+                                    float2 *work, float2 *spectrum, uint32_t count, cudaStream_t st)
+{
+    return launch_fft(p, PASS2_SPECTRUM, in, 0, n_steps, mean, work, reinterpret_cast<float *>(spectrum), 0, count, 1.0f, 1, st, NULL);
+}
+
+// out[2k] = scale * Re Z[k], out[2k+1] = -scale * Im Z[k] for k < pairs, Z = complex transform of the n/2 complex points in `in`
+cudaError_t brp_launch_fft_conj(const BrpFftPlan &p, const float2 *in, const uint32_t *n_steps_full, const float *mean,
+                                float2 *work, float *out, uint32_t pairs, float scale, cudaStream_t st)
+{
+    return launch_fft(p, PASS2_CONJ, reinterpret_cast<const float *>(in), 0, n_steps_full, mean, work, out, 0, pairs, scale, 1, st, NULL);
 }

@@ -1,0 +1,201 @@
+// Whitening pre-step of a work-unit on the GPU: demod_binary.c:858-1079.
+//
+// Once per work-unit, before the template loop, the reference
+//   1. zero-pads the series to N = padding*Nu samples and takes its real FFT            (:905-926)
+//   2. forms the periodogram |X_k|^2 (DC excluded)                                      (:939)
+//   3. takes a running median over `window` bins (rngmed.c:48)                          (:953)
+//   4. scales X_{i+window/2} by sqrt(ln 2 / median_i)                                   (:964-969)
+//   5. replaces zap-list bins by Gaussian noise (GSL taus2 + ziggurat)                  (:982-1033)
+//   6. zeroes window/2 bins at either end, transforms back, multiplies by 1/sqrt(N)     (:1038-1069)
+// Steps 1-4 and 6 are done here with the library's own FFT kernels (fft.cu) and an exact sliding median;
+// step 5 needs GSL's ziggurat tables for bit parity, which are not in the reference tree, so a non-empty
+// zap list is not supported (the caller gets RADPUL_EVAL and can fall back to an unzapped search).
+//
+// The median is exact (same order statistics as rngmed.c, even windows average the two middle values in
+// double like rngmed.c:179,329): every output bin selects its k-th smallest window value by bisection on the
+// bit pattern of the non-negative floats, with the window staged in shared memory.
+#include <math.h>
+#include <stdio.h>
+
+#include "brp_internal.h"
+
+namespace {
+
+constexpr int kMedThreads = 256;
+
+__global__ void periodogram_kernel(const float2 *__restrict__ X, float *__restrict__ ps, uint32_t f)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= f) return;
+    const float2 v = X[i];
+    // gsl_pow_2(re) + gsl_pow_2(im) in double, rounded once (:939); the DC bin stays 0 (calloc + loop from 1)
+    ps[i] = i == 0 ? 0.0f : (float)((double)v.x * (double)v.x + (double)v.y * (double)v.y);
+}
+
+// k-th smallest (0-based) of win[0..n) for non-negative floats: bisection on the bit pattern
+__device__ __forceinline__ uint32_t select_kth(const uint32_t *__restrict__ win, int n, int k)
+{
+    uint32_t x = 0;
+    for (int bit = 30; bit >= 0; --bit) {
+        const uint32_t cand = x | (1u << bit);
+        int cnt = 0;
+        for (int j = 0; j < n; ++j) cnt += (win[j] < cand);
+        if (cnt <= k) x = cand;
+    }
+    return x;
+}
+
+__global__ void __launch_bounds__(kMedThreads)
+running_median_kernel(const float *__restrict__ ps, uint32_t length, uint32_t bsize, float *__restrict__ med, uint32_t n_out)
+{
+    extern __shared__ uint32_t sw[]; // kMedThreads + bsize - 1 values as bit patterns
+    const uint32_t first = blockIdx.x * kMedThreads;
+    const uint32_t span = kMedThreads + bsize - 1;
+    for (uint32_t j = threadIdx.x; j < span; j += kMedThreads) {
+        const uint32_t src = first + j;
+        sw[j] = src < length ? __float_as_uint(ps[src]) : 0x7F800000u; // +inf beyond the end (never selected)
+    }
+    __syncthreads();
+    const uint32_t i = first + threadIdx.x;
+    if (i >= n_out) return;
+    const uint32_t *win = sw + threadIdx.x; // consecutive threads read consecutive words: conflict-free
+    const int mid = (int)((bsize + (bsize & 1u)) / 2u) - 1; // rngmed.c:104
+    const uint32_t a = select_kth(win, (int)bsize, mid);
+    if (bsize & 1u) {
+        med[i] = __uint_as_float(a);
+        return;
+    }
+    // even window: the next order statistic is a itself if it occurs more than once above rank mid, else the
+    // smallest value greater than a
+    int le = 0;
+    uint32_t nxt = 0x7F800000u;
+    for (uint32_t j = 0; j < bsize; ++j) {
+        const uint32_t v = win[j];
+        le += (v <= a);
+        if (v > a && v < nxt) nxt = v;
+    }
+    const uint32_t bb = (le >= mid + 2) ? a : nxt;
+    med[i] = (float)((double)(__uint_as_float(a) + __uint_as_float(bb)) / 2.0); // float add, double halving (rngmed.c:179)
+}
+
+// steps 4 and the zeroing of step 6
+__global__ void scale_and_edge_kernel(float2 *__restrict__ X, const float *__restrict__ med, uint32_t f, uint32_t window_2,
+                                      uint32_t white_size)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= f) return;
+    float2 v = X[k];
+    if (k >= window_2 && k - window_2 < white_size) {
+        const float factor = (float)sqrt(M_LN2 / (double)med[k - window_2]); // :966
+        v.x *= factor;
+        v.y *= factor;
+    }
+    if (k < window_2 || k + window_2 >= f) v = make_float2(0.f, 0.f); // :1038-1044
+    X[k] = v;
+}
+
+// backward real transform of X[0..M] as one complex transform of length M:
+//   Z'[k] = (X[k] + conj X[M-k]) + i W_N^{-k} (X[k] - conj X[M-k]),   x = conj(FFT(conj Z')) interleaved
+__global__ void inverse_prep_kernel(const float2 *__restrict__ X, float2 *__restrict__ zc, uint32_t m, float two_over_n)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    const float2 a = X[k], b = X[m - k];
+    const float2 s = make_float2(a.x + b.x, a.y - b.y);
+    const float2 d = make_float2(a.x - b.x, a.y + b.y);
+    float sn, cs;
+    sincospif((float)k * two_over_n, &sn, &cs); // W_N^{-k} = exp(+2 pi i k / N)
+    const float2 wd = make_float2(cs * d.x - sn * d.y, cs * d.y + sn * d.x);
+    zc[k] = make_float2(s.x - wd.y, -(s.y + wd.x));
+}
+
+} // namespace
+
+#define WH_TRY(call, code)                                                                                   \
+    do {                                                                                                     \
+        cudaError_t e_ = (call);                                                                             \
+        if (e_ != cudaSuccess) {                                                                             \
+            fprintf(stderr, "[brp_b200] %s failed: %s (%s:%d)\n", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            rc = (code);                                                                                     \
+            goto done;                                                                                       \
+        }                                                                                                    \
+    } while (0)
+
+extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
+                                 uint32_t n_zap_ranges, float *device_ms)
+{
+    if (!series || nsamples_unpadded < 2 || padding < 1.0f || padding > 10.0f) return RADPUL_EVAL;
+    if (n_zap_ranges != 0) {
+        fprintf(stderr, "[brp_b200] brp_whiten_series: zap-list noise replacement is not supported "
+                        "(it needs GSL's ziggurat tables for parity with demod_binary.c:1012-1021)\n");
+        return RADPUL_EVAL;
+    }
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) return RADPUL_CUDA_DEVICE_FIND;
+    if (cudaSetDevice(device) != cudaSuccess) return RADPUL_CUDA_DEVICE_SET;
+
+    const uint32_t nu = nsamples_unpadded;
+    const uint32_t n = (uint32_t)(int)(padding * nu + 0.5);                 // demod_binary.c:782
+    const uint32_t window_2 = (uint32_t)(int)(0.5 * window + 0.5);          // :869
+    const uint32_t f = (uint32_t)(0.5 * n + 0.5) + 1;                       // :875
+    if (f < window || window == 0) return RADPUL_EVAL;                       // :878-882
+    if (window > 16384) return RADPUL_EVAL;                                  // shared-memory staging of the median window
+    const uint32_t white_size = f - window + 1;
+    const uint32_t m = n / 2;
+
+    int rc = 0;
+    BrpFftPlan plan;
+    float *d_x = NULL, *d_ps = NULL, *d_med = NULL, *d_out = NULL, *d_mean = NULL;
+    float2 *d_X = NULL, *d_zc = NULL, *d_work = NULL;
+    uint32_t *d_ns = NULL;
+    cudaEvent_t ev0 = NULL, ev1 = NULL;
+    cudaStream_t st = 0;
+    memset(&plan, 0, sizeof(plan));
+    rc = brp_fft_plan_create(&plan, n);
+    if (rc) return rc;
+    {
+        const uint32_t ns_host[2] = {nu, n};
+        const float zero = 0.0f;
+        const size_t nu4 = ((size_t)nu + 3) & ~(size_t)3;
+        const int med_smem = (int)((kMedThreads + window - 1) * sizeof(uint32_t));
+        WH_TRY(cudaMalloc((void **)&d_x, sizeof(float) * nu4), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_X, sizeof(float2) * ((size_t)m + 2)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_zc, sizeof(float2) * (size_t)m), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_work, sizeof(float2) * (size_t)m), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_ps, sizeof(float) * (size_t)f), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_med, sizeof(float) * (size_t)white_size), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_out, sizeof(float) * (nu4 + 4)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_ns, sizeof(uint32_t) * 2), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaMalloc((void **)&d_mean, sizeof(float)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+        WH_TRY(cudaEventCreate(&ev0), RADPUL_CUDA_DEVICE_SET);
+        WH_TRY(cudaEventCreate(&ev1), RADPUL_CUDA_DEVICE_SET);
+        WH_TRY(cudaMemcpy(d_x, series, sizeof(float) * nu, cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+        WH_TRY(cudaMemcpy(d_ns, ns_host, sizeof(ns_host), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+        WH_TRY(cudaMemcpy(d_mean, &zero, sizeof(float), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+        if (med_smem > 48 * 1024)
+            WH_TRY(cudaFuncSetAttribute((const void *)running_median_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, med_smem),
+                   RADPUL_CUDA_KERNEL_INVOKE);
+        cudaEventRecord(ev0, st);
+        // 1. forward transform of the zero-padded series: samples >= Nu read as 0 (never materialised)
+        WH_TRY(brp_launch_fft_spectrum(plan, d_x, d_ns, d_mean, d_work, d_X, m + 1, st), RADPUL_CUDA_FFT_EXEC);
+        // 2.-4. periodogram, running median, rescale, zero the edges
+        periodogram_kernel<<<(f + 255) / 256, 256, 0, st>>>(d_X, d_ps, f);
+        running_median_kernel<<<(white_size + kMedThreads - 1) / kMedThreads, kMedThreads, med_smem, st>>>(d_ps, f, window, d_med, white_size);
+        scale_and_edge_kernel<<<(f + 255) / 256, 256, 0, st>>>(d_X, d_med, f, window_2, white_size);
+        // 6. backward transform and renormalisation: 1/sqrt((float)N) held in a float (:1066)
+        inverse_prep_kernel<<<(m + 255) / 256, 256, 0, st>>>(d_X, d_zc, m, 2.0f / (float)n);
+        WH_TRY(cudaGetLastError(), RADPUL_CUDA_KERNEL_INVOKE);
+        const float norm_factor = (float)(1.0 / sqrt((double)(float)n));
+        WH_TRY(brp_launch_fft_conj(plan, d_zc, d_ns + 1, d_mean, d_work, d_out, (nu + 1) / 2, norm_factor, st), RADPUL_CUDA_FFT_EXEC);
+        cudaEventRecord(ev1, st);
+        WH_TRY(cudaMemcpy(series, d_out, sizeof(float) * nu, cudaMemcpyDeviceToHost), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
+        if (device_ms) cudaEventElapsedTime(device_ms, ev0, ev1);
+    }
+done:
+    cudaFree(d_x); cudaFree(d_X); cudaFree(d_zc); cudaFree(d_work); cudaFree(d_ps); cudaFree(d_med); cudaFree(d_out);
+    cudaFree(d_ns); cudaFree(d_mean);
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    brp_fft_plan_destroy(&plan);
+    return rc;
+}

@@ -242,6 +242,14 @@ int brp_stage_harmonic_summing(brp_search *s, const float *host_ps, const float 
 int brp_stage_sin_lut(int device, const float *x, float *sin_out, uint32_t n);
 int brp_stage_round_index(int device, const float *f, int32_t *idx_out, uint32_t n);
 
+/* Whitening pre-step of a work-unit (demod_binary.c:858-1079, once per work-unit, before the template loop): FFT of the
+ * zero-padded series, periodogram, exact running median over `window` bins (rngmed.c:48), rescaling to a white spectrum,
+ * zeroing of window/2 edge bins, back-transform, 1/sqrt(N).  `series` (HOST, nsamples_unpadded floats) is whitened in
+ * place.  The zap-list noise replacement (:982-1033) needs GSL's ziggurat generator and is not supported: n_zap_ranges
+ * must be 0 (RADPUL_EVAL otherwise).  device_ms (optional) receives the device time of the whole step. */
+int brp_whiten_series(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
+                      uint32_t n_zap_ranges, float *device_ms);
+
 /* =====================================================================================
  * 4. Resampling without any device allocation
  * ===================================================================================== */

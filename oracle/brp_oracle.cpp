@@ -424,4 +424,75 @@ int brp_oracle_search(const float *series, const brp_oracle_geometry *g, float f
     return rc;
 }
 
+/* rngmed.c:48-341 computes the same numbers with a linked list and checkpoints; here: a sorted window */
+int brp_oracle_rngmed(const float *input, uint32_t length, uint32_t bsize, float *medians)
+{
+    if (bsize == 0 || bsize > length) return 4;
+    float *win = (float *)malloc(sizeof(float) * bsize);
+    if (!win) return 1;
+    memcpy(win, input, sizeof(float) * bsize);
+    qsort(win, bsize, sizeof(float), [](const void *a, const void *b) {
+        const float x = *(const float *)a, y = *(const float *)b;
+        return (x > y) - (x < y);
+    });
+    const uint32_t mid = (bsize + (bsize & 1)) / 2 - 1; /* rngmed.c:104 */
+    for (uint32_t i = 0;; i++) {
+        medians[i] = (bsize & 1) ? win[mid] : (float)((win[mid] + win[mid + 1]) / 2.0); /* rngmed.c:177-179,327-329 */
+        if (i + bsize >= length) break;
+        /* replace input[i] by input[i+bsize] keeping the window sorted */
+        const float oldv = input[i], newv = input[i + bsize];
+        uint32_t lo = 0, hi = bsize;
+        while (lo < hi) { const uint32_t m = (lo + hi) / 2; if (win[m] < oldv) lo = m + 1; else hi = m; }
+        uint32_t pos = lo; /* first element == oldv */
+        if (newv >= oldv) {
+            while (pos + 1 < bsize && win[pos + 1] < newv) { win[pos] = win[pos + 1]; pos++; }
+        } else {
+            while (pos > 0 && win[pos - 1] > newv) { win[pos] = win[pos - 1]; pos--; }
+        }
+        win[pos] = newv;
+    }
+    free(win);
+    return 0;
+}
+
+/* demod_binary.c:858-1079 with an empty zap list */
+int brp_oracle_whiten(float *series, uint32_t n_unpadded, float padding, uint32_t window)
+{
+    uint32_t nsamples = n_unpadded;
+    nsamples = (int)(padding * nsamples + 0.5);
+    const unsigned int window_2 = (int)(0.5 * window + 0.5);
+    const unsigned int fft_size = (unsigned int)(0.5 * nsamples + 0.5) + 1;
+    if (fft_size < window) return 4;
+    drfft_plan *plan = drfft_plan_create(nsamples);
+    if (!plan) return 4;
+    float *time_series = (float *)calloc(nsamples, sizeof(float));
+    float *fft = (float *)malloc(sizeof(float) * 2 * fft_size);
+    float *ps = (float *)calloc(fft_size, sizeof(float));
+    const int white_size = fft_size - window + 1;
+    float *med = (float *)calloc(white_size, sizeof(float));
+    if (!time_series || !fft || !ps || !med) return 1;
+    for (uint32_t i = 0; i < n_unpadded; i++) time_series[i] = series[i];
+    drfft_execute_f32(plan, time_series, fft);
+    for (unsigned int i = 1; i < fft_size; i++) {
+        const double re = fft[2 * i], im = fft[2 * i + 1];
+        ps[i] = re * re + im * im;
+    }
+    brp_oracle_rngmed(ps, fft_size, window, med);
+    for (int i = 0; i < white_size; i++) {
+        float factor = sqrt(M_LN2 / med[i]);
+        fft[2 * (i + window_2)] *= factor;
+        fft[2 * (i + window_2) + 1] *= factor;
+    }
+    for (unsigned int i = 0; i < window_2; i++) {
+        fft[2 * i] = fft[2 * i + 1] = 0.0f;
+        fft[2 * (fft_size - i - 1)] = fft[2 * (fft_size - i - 1) + 1] = 0.0f;
+    }
+    drfft_execute_c2r_f32(plan, fft, time_series);
+    const float norm_factor = 1.0 / sqrt((float)nsamples);
+    for (uint32_t i = 0; i < n_unpadded; i++) series[i] = norm_factor * time_series[i];
+    free(time_series); free(fft); free(ps); free(med);
+    drfft_plan_destroy(plan);
+    return 0;
+}
+
 } /* extern "C" */

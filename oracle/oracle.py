@@ -81,6 +81,8 @@ class Oracle:
         L.brp_oracle_base_thresholds.argtypes = [C.c_float, C.c_uint32, f32p]
         L.brp_oracle_finalize.argtypes = [C.c_void_p, C.c_void_p]
         L.brp_oracle_format_candidates.argtypes = [C.c_void_p, C.POINTER(Geometry), C.c_double, C.c_char_p, C.c_int]
+        L.brp_oracle_whiten.argtypes = [f32p, C.c_uint32, C.c_float, C.c_uint32]
+        L.brp_oracle_rngmed.argtypes = [f32p, C.c_uint32, C.c_uint32, f32p]
         L.brp_oracle_search.argtypes = [f32p, C.POINTER(Geometry), C.c_float, f64p, C.c_uint32, C.c_void_p, C.c_void_p]
 
     def geometry(self, nu: int, tsample_us: float, padding: float, f0: float, window: int) -> Geometry:
@@ -128,6 +130,18 @@ class Oracle:
         thr = np.empty(5, np.float32)
         self.L.brp_oracle_base_thresholds(fA, fft_size, thr)
         return thr
+
+    def whiten(self, series: np.ndarray, padding: float, window: int) -> np.ndarray:
+        out = np.ascontiguousarray(series, np.float32).copy()
+        rc = self.L.brp_oracle_whiten(out, out.size, padding, window)
+        assert rc == 0
+        return out
+
+    def rngmed(self, data: np.ndarray, window: int) -> np.ndarray:
+        data = np.ascontiguousarray(data, np.float32)
+        out = np.empty(len(data) - window + 1, np.float32)
+        assert self.L.brp_oracle_rngmed(data, len(data), window, out) == 0
+        return out
 
     def search(self, series: np.ndarray, g: Geometry, fA: float, bank: np.ndarray):
         bank = np.ascontiguousarray(bank, np.float64)

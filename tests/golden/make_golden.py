@@ -7,7 +7,8 @@ The inputs are regenerated from the seed by the tests, so only outputs are store
 Cases
   A  Nu = 2^14, padding 1.0  : index array, n_steps, resampled series, spectrum, summed spectra, dirty pages
   B  Nu = 2^14, padding 3.0  : same taps for the 3*2^n FFT length
-  C  Nu = 2^16, 12-template bank through the unmodified reference driver (demod_binary.c MAIN): candidate file
+  C  Nu = 2^16, 12-template bank through the unmodified reference driver (demod_binary.c MAIN): candidate file,
+     without and with the whitening pre-step (-W, empty zap list)
 """
 import sys
 import tempfile
@@ -70,6 +71,12 @@ def main():
                                    "-f", "400", "-A", "0.08", "-P", padding, "-B", "200"])
             assert r.returncode == 0, r.stderr
             out[f"{tag}_candfile"] = np.frombuffer(open(d + f"/{tag}.cand", "rb").read(), np.uint8)
+            # the same run with the whitening pre-step (-W) and an EMPTY zap list (no GSL noise draws)
+            open(d + "/zap.txt", "w").close()
+            r = Reference.run_cli(["-i", d + "/wu.binary", "-o", d + f"/{tag}W.cand", "-t", d + "/bank.txt", "-c", d + f"/{tag}W.cpt",
+                                   "-l", d + "/zap.txt", "-f", "400", "-A", "0.08", "-P", padding, "-B", "200", "-W"])
+            assert r.returncode == 0, r.stderr
+            out[f"{tag}W_candfile"] = np.frombuffer(open(d + f"/{tag}W.cand", "rb").read(), np.uint8)
     out["C_bank"] = bank
     np.savez_compressed(Path(__file__).parent / "golden_v1.npz", **out)
     print("wrote golden_v1.npz with", len(out), "arrays")

@@ -122,3 +122,24 @@ def test_geometry_table(oracle):
     for nu, pad, want in rows:
         g = oracle.geometry(nu, synth.TSAMPLE_US, pad, 400.0, 1000)
         assert (g.nsamples, g.fft_size, g.window_2, g.fundamental_idx_hi, g.harmonic_idx_hi) == want
+
+
+@pytest.mark.parametrize("tag,padding", [("C1W", 1.0), ("C3W", 3.0)])
+def test_oracle_whitening_matches_golden_candidate_file(oracle, golden, tag, padding):
+    """Whitening pre-step (demod_binary.c:858-1079, empty zap list) restated in the oracle: the reference driver run with
+    -W produced these candidate files."""
+    series, _ = golden_case_C()
+    bank = golden["C_bank"]
+    g = oracle.geometry(1 << 16, synth.TSAMPLE_US, padding, 400.0, 200)
+    white = oracle.whiten(series, padding, 200)
+    cands, tidx = oracle.search(white, g, 0.08, bank)
+    cf, _ = oracle.finalize(cands, tidx)
+    assert oracle.format_candidates(cf, g, synth.TSAMPLE_US) == bytes(golden[f"{tag}_candfile"]).decode()
+
+
+def test_oracle_running_median_matches_reference(oracle, reference):
+    rng = np.random.default_rng(8)
+    x = rng.exponential(1.0, 6000).astype(np.float32)
+    x[100:140] = x[100]                       # ties
+    for window in (3, 10, 11, 100, 1000, 1001):
+        assert np.array_equal(bits(oracle.rngmed(x, window)), bits(reference.rngmed(x, window)))
