@@ -85,7 +85,7 @@ EXPORTED_SYMBOLS = [
     "tear_down_fft", "set_up_harmonic_summing", "run_harmonic_summing", "tear_down_harmonic_summing", "shutdown_cuda",
     "brp_derive_geometry", "brp_derive_template", "brp_base_thresholds", "brp_chisq_Q", "brp_chisq_Qinv",
     "brp_bank_read", "brp_bank_free", "brp_wu_read", "brp_series_free", "brp_toplist_from_hits",
-    "brp_finalize_candidates", "brp_format_candidates", "brp_write_candidates", "brp_checkpoint_write",
+    "brp_toplist_merge", "brp_finalize_candidates", "brp_format_candidates", "brp_write_candidates", "brp_checkpoint_write",
     "brp_checkpoint_read", "brp_search_create", "brp_search_destroy", "brp_search_set_series",
     "brp_search_set_series_device", "brp_search_reset", "brp_search_run", "brp_search_sync", "brp_search_collect",
     "brp_search_last_run_ms", "brp_search_stream", "brp_search_kernel_launches", "brp_search_profile_batch",
@@ -123,6 +123,7 @@ lib.brp_wu_read.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINT
 lib.brp_series_free.argtypes = [C.POINTER(C.c_float)]
 lib.brp_series_free.restype = None
 lib.brp_toplist_from_hits.argtypes = [C.c_void_p, C.c_uint32, _f64, C.c_uint32, C.c_void_p, C.c_void_p]
+lib.brp_toplist_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
 lib.brp_finalize_candidates.argtypes = [C.c_void_p, C.c_void_p]
 lib.brp_format_candidates.argtypes = [C.c_void_p, C.POINTER(Geometry), C.c_double, C.c_char_p, C.c_int]
 lib.brp_write_candidates.argtypes = [C.c_char_p, C.c_void_p, C.POINTER(Geometry), C.c_double]
@@ -215,6 +216,13 @@ def toplist_from_hits(hits: np.ndarray, bank: np.ndarray):
     _check(lib.brp_toplist_from_hits(hits.ctypes.data, len(hits), bank, bank.shape[0], cands.ctypes.data, tidx.ctypes.data),
            "brp_toplist_from_hits")
     return cands, tidx
+
+
+def toplist_merge(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    a, b = np.ascontiguousarray(a, CAND_DTYPE), np.ascontiguousarray(b, CAND_DTYPE)
+    out = np.zeros(N_CAND, CAND_DTYPE)
+    _check(lib.brp_toplist_merge(a.ctypes.data, b.ctypes.data, out.ctypes.data), "brp_toplist_merge")
+    return out
 
 
 def finalize_candidates(cands: np.ndarray, tidx: np.ndarray):

@@ -12,6 +12,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "libbrp_b200.so"
+CLI = HERE / "brp_b200_search"  # command-line driver over the batched API (csrc/brp_search_main.cpp)
 SOURCES = ["resamp.cu", "fft.cu", "hs.cu", "search.cu", "legacy.cu", "noalloc.cu", "whiten.cu", "host.cpp"]
 HEADERS = ["brp_internal.h", "brp_device.cuh", "../../include/brp_b200.h"]
 NVCC_FLAGS = [
@@ -55,6 +56,11 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     if force or procs or _stale(LIB, objs):
         cmd = [nvcc, "-shared", "-o", str(LIB)] + [str(o) for o in objs] + ["-lz", "-lcudart"]
         subprocess.run(cmd, check=True)
+    main = CSRC / "brp_search_main.cpp"
+    if force or _stale(CLI, [main, LIB, (CSRC / "../../include/brp_b200.h").resolve()]):
+        cxx = os.environ.get("CXX", "g++")
+        subprocess.run([cxx, "-O2", "-std=c++17", str(main), "-o", str(CLI), f"-L{HERE}", "-lbrp_b200",
+                        "-Wl,-rpath,$ORIGIN", "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"], check=True)
     return LIB
 
 

@@ -1,0 +1,282 @@
+// brp_b200_search: command-line driver over the BATCHED API of libbrp_b200.so.
+//
+// Same command line, input formats, candidate file and checkpoint file as the reference's standalone driver
+// (demod_binary.c MAIN: options :217-470, work-unit :655-842, loop :1180-1443, results :1502-1686, checkpoint
+// :1743-1783 / resume :560-652), but the template loop is brp_search_run() over whole chunks of the bank instead of
+// one run_resampling/run_fft/run_harmonic_summing round trip per template.  (The unmodified reference driver linked
+// against the eleven legacy symbols is the other way to run this library; see INTEGRATION.md.)
+//
+// There is no CPU path in here: every stage of the search runs in the CUDA kernels of the library, and the program
+// fails with the library's RADPUL_* code when no device is usable.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../include/brp_b200.h"
+
+namespace {
+
+struct Options {
+    const char *input = nullptr, *output = nullptr, *bank = nullptr, *checkpoint = nullptr, *zaplist = nullptr;
+    int white = 0, device = 0, debug = 0;
+    float f0 = 250.0f, padding = 1.0f, fA = 0.04f; /* defaults of demod_binary.c:204-215 */
+    unsigned window = 1000;
+    unsigned chunk = 2048;            /* templates per brp_search_run between checkpoint opportunities */
+    double checkpoint_period_s = 60;  /* wall-clock seconds between checkpoints (0 = after every chunk) */
+    long max_templates = -1;          /* stop (with a checkpoint) after this many templates of this invocation */
+    unsigned batch = 16;              /* templates per kernel launch */
+};
+
+void usage(const char *argv0)
+{
+    printf("Usage: %s [options]\n"
+           " -i, --input_file       string  work-unit (.bin4 or .binary, zlib or plain)\n"
+           " -o, --output_file      string  candidate file\n"
+           " -t, --template_bank    string  template bank (P tau Psi0 per line)\n"
+           " -c, --checkpoint_file  string  checkpoint file (read on start if present)\n"
+           " -l, --zaplist_file     string  zap list (only an EMPTY list is supported with -W)\n"
+           " -f, --f0               float   maximum signal frequency in Hz (default 250)\n"
+           " -A, --false_alarm      float   false alarm probability (default 0.04)\n"
+           " -P, --padding          float   padding factor (default 1.0)\n"
+           " -W, --whitening                whiten the series first\n"
+           " -B, --box              int     running-median window (default 1000)\n"
+           " -D, --device           int     CUDA device (default 0)\n"
+           " -z, --debug                    more output\n"
+           "     --chunk            int     templates per enqueue between checkpoint opportunities (default 2048)\n"
+           "     --batch            int     templates per kernel launch (default 16)\n"
+           "     --checkpoint_period float  seconds between checkpoints (default 60; 0 = every chunk)\n"
+           "     --max_templates    int     stop after this many templates, leaving a checkpoint\n",
+           argv0);
+}
+
+bool is(const char *a, const char *s, const char *l) { return strcmp(a, s) == 0 || strcmp(a, l) == 0; }
+
+int parse(int argc, char **argv, Options &o)
+{
+    for (int i = 1; i < argc;) {
+        const char *a = argv[i];
+        const bool has_val = i + 1 < argc;
+        const char *v = has_val ? argv[i + 1] : "";
+        if (is(a, "-W", "--whitening")) { o.white = 1; i++; continue; }
+        if (is(a, "-z", "--debug")) { o.debug = 1; i++; continue; }
+        if (is(a, "-h", "--help")) { usage(argv[0]); return RADPUL_EMISC; }
+        if (!has_val) {
+            fprintf(stderr, "Option %s needs a value.\n", a);
+            return RADPUL_EMISC;
+        }
+        if (is(a, "-P", "--padding")) {
+            if (atof(v) < 1.0 || atof(v) > 10.0) {
+                fprintf(stderr, "Nonsense value: padding factor %g.\n", atof(v));
+                return RADPUL_EVAL;
+            }
+            o.padding = atof(v);
+        } else if (is(a, "-B", "--box")) {
+            if (atoi(v) < 0 || atoi(v) > 250000) {
+                fprintf(stderr, "Nonsense value: window size for running median %d.\n", atoi(v));
+                return RADPUL_EVAL;
+            }
+            o.window = atoi(v);
+        } else if (is(a, "-f", "--f0")) {
+            if (atof(v) < 0.0 || atof(v) > 16.0e3) {
+                fprintf(stderr, "Nonsense value: upper limit for search frequency %g.\n", atof(v));
+                return RADPUL_EVAL;
+            }
+            o.f0 = atof(v);
+        } else if (is(a, "-A", "--false_alarm")) {
+            if (atof(v) < 0.0 || atof(v) > 1.0) {
+                fprintf(stderr, "Nonsense value: false alarm rate %g.\n", atof(v));
+                return RADPUL_EVAL;
+            }
+            o.fA = atof(v);
+        } else if (is(a, "-i", "--input_file")) {
+            if (!strstr(v, ".binary") && !strstr(v, ".bin4")) {
+                fprintf(stderr, "Unknown file format (extension) for input file: %s\n", v);
+                return RADPUL_EFILE;
+            }
+            o.input = v;
+        } else if (is(a, "-o", "--output_file")) o.output = v;
+        else if (is(a, "-c", "--checkpoint_file")) o.checkpoint = v;
+        else if (is(a, "-t", "--template_bank")) o.bank = v;
+        else if (is(a, "-l", "--zaplist_file")) o.zaplist = v;
+        else if (is(a, "-D", "--device")) {
+            if (atoi(v) < 0) {
+                fprintf(stderr, "Nonsense value: device %d.\n", atoi(v));
+                return RADPUL_EVAL;
+            }
+            o.device = atoi(v);
+        } else if (strcmp(a, "--chunk") == 0) o.chunk = std::max(1, atoi(v));
+        else if (strcmp(a, "--batch") == 0) o.batch = std::max(1, atoi(v));
+        else if (strcmp(a, "--checkpoint_period") == 0) o.checkpoint_period_s = atof(v);
+        else if (strcmp(a, "--max_templates") == 0) o.max_templates = atol(v);
+        else {
+            fprintf(stderr, "Unknown option: %s\n", a);
+            usage(argv[0]);
+            return RADPUL_EMISC;
+        }
+        i += 2;
+    }
+    if (!o.input || !o.output || !o.bank) {
+        fprintf(stderr, "Input file, output file and template bank are required.\n");
+        return RADPUL_EMISC;
+    }
+    return 0;
+}
+
+/* number of non-comment lines of the zap list; the reference reads "%lg %lg" pairs (demod_binary.c:993-1023) */
+int count_zap_ranges(const char *path, unsigned *n)
+{
+    *n = 0;
+    FILE *f = fopen(path, "r");
+    if (!f) return RADPUL_EFILE;
+    char line[256];
+    while (fgets(line, sizeof line, f)) {
+        double a, b;
+        if (sscanf(line, "%lg %lg", &a, &b) == 2) ++*n;
+    }
+    fclose(f);
+    return 0;
+}
+
+double now_s()
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
+
+}  // namespace
+
+#define CHECK(call)                                                              \
+    do {                                                                         \
+        int rc_ = (call);                                                        \
+        if (rc_ != 0) {                                                          \
+            fprintf(stderr, "%s failed with code %d (%s:%d)\n", #call, rc_, __FILE__, __LINE__); \
+            return rc_;                                                          \
+        }                                                                        \
+    } while (0)
+
+int main(int argc, char **argv)
+{
+    Options o;
+    int rc = parse(argc, argv, o);
+    if (rc) return rc;
+
+    /* ---- resume: demod_binary.c:560-652 ---- */
+    uint32_t done = 0;
+    bool resumed = false;
+    std::vector<brp_cand> carried(BRP_N_CAND);
+    memset(carried.data(), 0, sizeof(brp_cand) * BRP_N_CAND);
+    if (o.checkpoint) {
+        char original[256] = {0};
+        FILE *probe = fopen(o.checkpoint, "rb");
+        if (probe) {
+            fclose(probe);
+            CHECK(brp_checkpoint_read(o.checkpoint, &done, original, carried.data()));
+            if (strcmp(original, o.input) != 0) {
+                fprintf(stderr, "Input file on command line %s doesn't agree with input file %s from checkpoint header.\n",
+                        o.input, original);
+                return RADPUL_EVAL;
+            }
+            resumed = true;
+            fprintf(stderr, "Continuing work on %s at template no. %u\n", original, done);
+        }
+    }
+
+    /* ---- work-unit and bank ---- */
+    float *series = nullptr;
+    uint32_t nu = 0;
+    double tsample_us = 0;
+    CHECK(brp_wu_read(o.input, &series, &nu, &tsample_us));
+    double *bank = nullptr;
+    uint32_t n_templates = 0;
+    CHECK(brp_bank_read(o.bank, &bank, &n_templates));
+    if (done > n_templates) {
+        fprintf(stderr, "Checkpoint is ahead of the template bank (%u > %u).\n", done, n_templates);
+        return RADPUL_EVAL;
+    }
+    brp_geometry g;
+    CHECK(brp_derive_geometry(nu, tsample_us, o.padding, o.f0, o.window, &g));
+
+    /* ---- whitening, once per work-unit (demod_binary.c:858-1079) ---- */
+    if (o.white) {
+        unsigned n_zap = 0;
+        if (o.zaplist) CHECK(count_zap_ranges(o.zaplist, &n_zap));
+        float ms = 0;
+        CHECK(brp_whiten_series(o.device, series, nu, o.padding, o.window, n_zap, &ms));
+        if (o.debug) fprintf(stderr, "Whitening: %.2f ms on the device\n", ms);
+    }
+
+    /* ---- the template loop, chunk by chunk ---- */
+    brp_search *s = nullptr;
+    CHECK(brp_search_create(&s, o.device, &g, o.fA, o.batch));
+    CHECK(brp_search_set_series(s, series));
+    brp_series_free(series);
+
+    std::vector<brp_hit> hits(5u * g.fundamental_idx_hi + 1);
+    std::vector<brp_cand> fresh(BRP_N_CAND), merged(BRP_N_CAND);
+    /* candidates of everything searched so far: checkpoint content merged with this invocation's device table */
+    auto snapshot = [&](brp_cand *out) -> int {
+        uint32_t n_hits = 0;
+        int r = brp_search_collect(s, hits.data(), (uint32_t)hits.size(), &n_hits);
+        if (r) return r;
+        r = brp_toplist_from_hits(hits.data(), n_hits, bank, n_templates, fresh.data(), nullptr);
+        if (r) return r;
+        if (!resumed) {
+            memcpy(out, fresh.data(), sizeof(brp_cand) * BRP_N_CAND);
+            return 0;
+        }
+        return brp_toplist_merge(carried.data(), fresh.data(), out);
+    };
+
+    const double t_start = now_s();
+    double t_last_cp = t_start;
+    uint32_t pos = done;
+    long budget = o.max_templates;
+    bool stopped_early = false;
+    while (pos < n_templates) {
+        uint32_t n = std::min<uint32_t>(o.chunk, n_templates - pos);
+        if (budget >= 0) {
+            if (budget == 0) {
+                stopped_early = true;
+                break;
+            }
+            n = (uint32_t)std::min<long>(n, budget);
+            budget -= n;
+        }
+        CHECK(brp_search_run(s, bank + 3 * (size_t)pos, n, pos));
+        CHECK(brp_search_sync(s));
+        pos += n;
+        const bool last = pos == n_templates;
+        const bool due = o.checkpoint && !last && (now_s() - t_last_cp >= o.checkpoint_period_s || budget == 0);
+        if (due) {
+            CHECK(snapshot(merged.data()));
+            CHECK(brp_checkpoint_write(o.checkpoint, pos, o.input, merged.data()));
+            t_last_cp = now_s();
+            if (o.debug) fprintf(stderr, "Checkpoint at template %u\n", pos);
+        }
+    }
+    if (budget == 0 && pos < n_templates) stopped_early = true;
+    const double t_loop = now_s() - t_start;
+    if (o.debug)
+        fprintf(stderr, "%u templates in %.3f s (%.0f templates/s)\n", pos - done, t_loop, (pos - done) / std::max(t_loop, 1e-9));
+
+    if (stopped_early) {
+        fprintf(stderr, "Stopped after %u of %u templates%s.\n", pos, n_templates, o.checkpoint ? "; checkpoint written" : "");
+        brp_search_destroy(s);
+        brp_bank_free(bank);
+        return 0;
+    }
+
+    /* ---- results: demod_binary.c:1502-1686 ---- */
+    CHECK(snapshot(merged.data()));
+    if (o.checkpoint) CHECK(brp_checkpoint_write(o.checkpoint, n_templates, o.input, merged.data())); /* :1498 final checkpoint */
+    CHECK(brp_finalize_candidates(merged.data(), nullptr));
+    CHECK(brp_write_candidates(o.output, merged.data(), &g, tsample_us));
+    CHECK(brp_search_destroy(s));
+    brp_bank_free(bank);
+    return 0;
+}

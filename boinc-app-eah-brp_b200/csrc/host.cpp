@@ -236,6 +236,38 @@ int brp_toplist_from_hits(const brp_hit *hits, uint32_t n_hits, const double *ba
     return 0;
 }
 
+/* Merge two candidate arrays in the "right after the loop" state (e.g. a checkpoint and the hits of the templates searched
+ * since): per harmonic, one entry per bin (the stronger; `a` wins ties, it is the earlier part of the bank), the 100
+ * strongest kept, descending power.  Exact for resuming: a bin that missed the first part's top 100 cannot re-enter
+ * through a weaker later value. */
+int brp_toplist_merge(const brp_cand a[BRP_N_CAND], const brp_cand b[BRP_N_CAND], brp_cand out[BRP_N_CAND])
+{
+    if (!a || !b || !out) return RADPUL_EVAL;
+    std::vector<brp_cand> res(BRP_N_CAND);
+    memset(res.data(), 0, sizeof(brp_cand) * BRP_N_CAND);
+    for (int k = 0; k < 5; k++) {
+        std::vector<brp_cand> v;
+        for (int i = 0; i < BRP_N_CAND_5; i++)
+            if (a[k * BRP_N_CAND_5 + i].power > 0.0) v.push_back(a[k * BRP_N_CAND_5 + i]);
+        const size_t na = v.size();
+        for (int i = 0; i < BRP_N_CAND_5; i++) {
+            const brp_cand &c = b[k * BRP_N_CAND_5 + i];
+            if (!(c.power > 0.0)) continue;
+            bool dup = false;
+            for (size_t j = 0; j < na && !dup; j++)
+                if (v[j].f0 == c.f0) {
+                    if (c.power > v[j].power) v[j] = c;
+                    dup = true;
+                }
+            if (!dup) v.push_back(c);
+        }
+        std::stable_sort(v.begin(), v.end(), [](const brp_cand &x, const brp_cand &y) { return x.power > y.power; });
+        for (size_t i = 0; i < v.size() && i < BRP_N_CAND_5; i++) res[k * BRP_N_CAND_5 + i] = v[i];
+    }
+    memcpy(out, res.data(), sizeof(brp_cand) * BRP_N_CAND);
+    return 0;
+}
+
 namespace {
 struct Tagged {
     brp_cand c;

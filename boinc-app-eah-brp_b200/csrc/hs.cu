@@ -17,13 +17,16 @@
 // table  key[k][j] = float_bits(power) << 32 | (0xFFFFFFFF - template index).
 // Above-threshold values are rare (false-alarm rate ~1e-7 per bin): nothing is written in the common case.
 //
-// Data movement.  A CTA owns kSpan consecutive bins i.  Harmonic l of those bins lives in ONE contiguous
-// slice of the spectrum, P[(l*i0+8)>>4 .. (l*i1+8)>>4] (about l*kSpan/16 floats), so the sixteen slices are
+// Data movement.  Work is cut into tiles of kSpan = 1024 consecutive bins i that START AT MULTIPLES OF kSpan
+// (the first tile of a template is partly below w2 and masked).  Harmonic l of a tile lives in ONE contiguous
+// slice of the spectrum, P[(l*i0+8)>>4 .. (l*i1+8)>>4] (l*kSpan/16 + 1 floats), so the sixteen slices are
 // brought into shared memory by sixteen 1-D bulk async copies (TMA, cp.async.bulk + mbarrier): no load
-// instructions, no registers, no L1 wavefronts on the way in.  Consecutive lanes then read consecutive or
-// identical shared-memory words (conflict-free, broadcast), and because a thread's bins are 256 apart,
-// the slice index of its next bin is the previous one plus the constant 16*l: one index computation per
-// harmonic and thread, immediate offsets afterwards.
+// instructions, no registers, no L1 wavefronts on the way in.  CTAs are persistent and walk the tiles of the
+// whole batch with a two-deep ring: warp 0 issues the copies of tile t+1 while all warps sum tile t.
+// Because i0 is a multiple of 1024, (l*i0+8)>>4 = l*i0/16 exactly, and the position of bin i0+tid+256*r inside
+// slice l is ((l*tid+8)>>4) + 16*l*r: a per-thread constant plus a compile-time offset.  The hot loop therefore
+// has no index arithmetic at all; consecutive lanes read consecutive or identical shared-memory words
+// (conflict-free, broadcast).
 // Algorithmic traffic 4*H bytes per template; the slices of different harmonics overlap in the spectrum,
 // so L2 serves 8.5*H floats per template and HBM about H.
 #include "brp_internal.h"

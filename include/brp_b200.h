@@ -178,6 +178,8 @@ typedef struct {
  * the template index of each slot (-1 = empty).  Hits from several GPUs may simply be concatenated. */
 int brp_toplist_from_hits(const brp_hit *hits, uint32_t n_hits, const double *bank, uint32_t n_templates,
                           brp_cand cands_out[BRP_N_CAND], int32_t *tmpl_idx_out);
+/* merge two candidate arrays that are in the state right after the loop (a = earlier part of the bank, e.g. a checkpoint) */
+int brp_toplist_merge(const brp_cand a[BRP_N_CAND], const brp_cand b[BRP_N_CAND], brp_cand out[BRP_N_CAND]);
 /* demod_binary.c:1502-1555: false-alarm statistic, power in sigma, sort by fA */
 int brp_finalize_candidates(brp_cand cands[BRP_N_CAND], int32_t *tmpl_idx_io);
 /* demod_binary.c:1632-1667: candidate lines + %DONE% into buf (returns bytes written, <0 on overflow).

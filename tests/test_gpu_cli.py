@@ -1,0 +1,94 @@
+"""brp_b200_search: the command-line driver over the batched API (row N3 of SURVEY.md 8f: work-unit ingest, chunked
+template loop, checkpoint/resume, candidate file) against the reference's own candidate files (tests/golden/)."""
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import brp_b200
+from brp_b200 import synth
+from helpers import golden_case_C
+
+pytestmark = pytest.mark.gpu
+
+EXE = Path(brp_b200.__file__).resolve().parent / "brp_b200_search"
+if not EXE.exists():  # brp_b200.py is an alias module at the repo root
+    EXE = Path(__file__).resolve().parent.parent / "boinc-app-eah-brp_b200" / "brp_b200_search"
+
+
+def run_cli(tmp, *extra, out="out.cand", cpt="cp.cpt", padding="1.0", check=True):
+    cmd = [str(EXE), "-i", str(tmp / "wu.binary"), "-o", str(tmp / out), "-t", str(tmp / "bank.txt"), "-f", "400", "-A", "0.08",
+           "-P", padding, "-B", "200", "-D", "0", "-z"]
+    if cpt:
+        cmd += ["-c", str(tmp / cpt)]
+    r = subprocess.run(cmd + list(extra), capture_output=True, text=True, timeout=600)
+    if check:
+        assert r.returncode == 0, r.stderr[-2000:]
+    return r
+
+
+@pytest.fixture()
+def wu(tmp_path, golden):
+    assert EXE.exists(), "brp_b200_search not built (python boinc-app-eah-brp_b200/build.py)"
+    _, q = golden_case_C()
+    synth.write_binary_wu(tmp_path / "wu.binary", q)
+    synth.write_bank(tmp_path / "bank.txt", golden["C_bank"])
+    return tmp_path
+
+
+def assert_same_candidates(got, ref):
+    assert len(got) == len(ref) and got[-1] == "%DONE%" and len(ref) > 5
+    for a, b in zip(got[:-1], ref[:-1]):
+        fa, fb = a.split(), b.split()
+        assert fa[:4] == fb[:4] and fa[6] == fb[6], (a, b)
+        assert abs(float(fa[4]) - float(fb[4])) <= 2e-4 * float(fb[4])           # power: the FFT tolerance of SURVEY.md 8c
+        assert abs(float(fa[5]) - float(fb[5])) <= 2e-3 * max(float(fb[5]), 1.0)  # -log10(fA)
+
+
+@pytest.mark.parametrize("tag,padding", [("C1", "1.0"), ("C3", "3.0")])
+def test_cli_reproduces_reference_candidate_file(wu, golden, tag, padding):
+    run_cli(wu, padding=padding)
+    got = (wu / "out.cand").read_text().splitlines()
+    assert_same_candidates(got, bytes(golden[f"{tag}_candfile"]).decode().splitlines())
+    n, name, cands = brp_b200.checkpoint_read(wu / "cp.cpt")          # final checkpoint, demod_binary.c:1498
+    assert n == len(golden["C_bank"]) and name.endswith("wu.binary") and np.count_nonzero(cands["power"]) > 5
+
+
+@pytest.mark.parametrize("stops", [(5,), (1, 4, 3)])
+def test_cli_interrupted_and_resumed_gives_the_same_file(wu, golden, stops):
+    run_cli(wu, out="whole.cand", cpt=None)
+    done = 0
+    for n in stops:                                # each invocation searches n more templates, then stops with a checkpoint
+        r = run_cli(wu, "--max_templates", str(n), "--chunk", "2", "--checkpoint_period", "0")
+        done += n
+        assert not (wu / "out.cand").exists()
+        assert brp_b200.checkpoint_read(wu / "cp.cpt")[0] == done, r.stderr
+    r = run_cli(wu, "--chunk", "3", "--checkpoint_period", "0")
+    assert f"at template no. {done}" in r.stderr
+    assert (wu / "out.cand").read_bytes() == (wu / "whole.cand").read_bytes()
+
+
+def test_cli_with_whitening(wu, golden):
+    (wu / "zap.txt").write_text("")
+    run_cli(wu, "-W", "-l", str(wu / "zap.txt"))
+    got = (wu / "out.cand").read_text().splitlines()
+    ref = bytes(golden["C1W_candfile"]).decode().splitlines()
+    key = lambda line: tuple(line.split()[:4] + [line.split()[6]])
+    assert got[-1] == "%DONE%" and [key(l) for l in got[:10]] == [key(l) for l in ref[:10]]
+    assert len({key(l) for l in got[:-1]} & {key(l) for l in ref[:-1]}) >= 0.9 * (len(ref) - 1)
+
+
+def test_cli_error_paths(wu):
+    run_cli(wu, "--max_templates", "2", "--checkpoint_period", "0")
+    (wu / "other.binary").write_bytes((wu / "wu.binary").read_bytes())
+    cmd = [str(EXE), "-i", str(wu / "other.binary"), "-o", str(wu / "o"), "-t", str(wu / "bank.txt"), "-c", str(wu / "cp.cpt")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+    assert r.returncode == brp_b200.RADPUL_EVAL and "doesn't agree" in r.stderr       # demod_binary.c:589-593
+    (wu / "zap.txt").write_text("60.0 0.1\n120.0 0.1\n")
+    r = run_cli(wu, "-W", "-l", str(wu / "zap.txt"), cpt=None, check=False)            # zap-list noise is not supported
+    assert r.returncode == brp_b200.RADPUL_EVAL
+    r = subprocess.run([str(EXE), "-i", "x.dat", "-o", "o", "-t", "t"], capture_output=True, text=True)
+    assert r.returncode == brp_b200.RADPUL_EFILE
+    r = subprocess.run([str(EXE), "-P", "0.5"], capture_output=True, text=True)
+    assert r.returncode == brp_b200.RADPUL_EVAL

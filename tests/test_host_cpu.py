@@ -238,3 +238,36 @@ def test_synthetic_series_is_reference_compatible(reference, tmp_path):
     got, _ = brp_b200.wu_read(tmp_path / "wu.binary")
     assert np.array_equal(got, series)
     assert abs(float(series.mean())) < 5e-3 and abs(float(series.std()) - 1.0) < 0.02
+
+
+def test_toplist_merge_resumes_exactly():
+    """Checkpoint resume in the batched driver (brp_b200_search): candidates of the first part of the bank merged with
+    the per-bin maxima of the rest must equal the candidates of the whole bank searched in one go (the reference keeps
+    one running toplist through demod_binary.c:1310-1397, checkpointed at :1423-1427)."""
+    rng = np.random.default_rng(5)
+    n_bins, n_t = 4000, 60
+    bank = np.column_stack([rng.uniform(600, 9000, n_t), rng.uniform(0, 1, n_t), rng.uniform(0, 6.28, n_t)])
+    for split in (1, 17, 59):
+        parts = []
+        for lo, hi in ((0, split), (split, n_t)):
+            hs = []
+            for k in range(5):
+                nb = 700 if k < 4 else 40                     # fewer than 100 hits for the last harmonic
+                b = rng.choice(np.arange(100, n_bins), nb, replace=False)
+                h = np.zeros(nb, brp_b200.HIT_DTYPE)
+                h["bin"], h["harm_idx"] = b, k
+                h["power"] = np.round(rng.gamma(3.0, 4.0, nb), 1).astype(np.float32) + 1   # coarse values: plenty of ties
+                h["tmpl"] = rng.integers(lo, hi, nb)
+                hs.append(h)
+            parts.append(np.concatenate(hs))
+        ca, _ = brp_b200.toplist_from_hits(parts[0], bank)
+        cb, _ = brp_b200.toplist_from_hits(parts[1], bank)
+        whole, _ = brp_b200.toplist_from_hits(np.concatenate(parts), bank)
+        merged = brp_b200.toplist_merge(ca, cb)
+        for k in range(5):
+            m, w = merged[100 * k:100 * k + 100], whole[100 * k:100 * k + 100]
+            assert np.array_equal(m["power"], w["power"])
+            # entries strictly above the rank-100 power are the same candidates (ties AT the boundary may pick another bin)
+            strict = w["power"] > w["power"][-1]
+            key = lambda c: sorted(zip(c["power"].tolist(), c["f0"].tolist(), c["P_b"].tolist(), c["tau"].tolist(), c["Psi"].tolist()))
+            assert key(m[strict]) == key(w[strict])
