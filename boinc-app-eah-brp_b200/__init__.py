@@ -89,7 +89,7 @@ EXPORTED_SYMBOLS = [
     "brp_checkpoint_read", "brp_search_create", "brp_search_destroy", "brp_search_set_series",
     "brp_search_set_series_device", "brp_search_reset", "brp_search_run", "brp_search_sync", "brp_search_collect",
     "brp_search_last_run_ms", "brp_search_stream", "brp_search_kernel_launches", "brp_search_profile_batch",
-    "brp_stage_resample", "brp_stage_spectrum", "brp_stage_spectrum_of", "brp_stage_harmonic_summing",
+    "brp_stage_resample", "brp_stage_resample_compare", "brp_stage_spectrum", "brp_stage_spectrum_of", "brp_stage_harmonic_summing",
     "brp_stage_sin_lut", "brp_stage_round_index", "brp_resample_noalloc", "brp_whiten_series",
 ]
 
@@ -144,6 +144,7 @@ lib.brp_search_kernel_launches.argtypes = [C.c_void_p]
 lib.brp_search_kernel_launches.restype = C.c_uint64
 lib.brp_search_profile_batch.argtypes = [C.c_void_p, _f64, C.c_uint32, C.c_uint32, _f32]
 lib.brp_stage_resample.argtypes = [C.c_void_p, C.POINTER(Template), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_float)]
+lib.brp_stage_resample_compare.argtypes = [C.c_void_p, _f64, C.c_uint32, C.POINTER(C.c_uint64)]
 lib.brp_stage_spectrum.argtypes = [C.c_void_p, _f32, C.c_uint32]
 lib.brp_stage_spectrum_of.argtypes = [C.c_void_p, _f32, _f32, C.c_uint32]
 lib.brp_stage_harmonic_summing.argtypes = [C.c_void_p, _f32, _f32, C.c_uint32, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
@@ -343,6 +344,13 @@ class Search:
         _check(lib.brp_stage_resample(self.h, C.byref(t), out.ctypes.data if want_series else None,
                                       idx.ctypes.data if want_index else None, C.byref(ns), C.byref(mean)), "brp_stage_resample")
         return out, idx, ns.value, mean.value
+
+    def stage_resample_compare(self, bank: np.ndarray) -> int:
+        """Number of index positions where the run-detecting resampler differs from per-sample evaluation (must be 0)."""
+        bank = np.ascontiguousarray(bank, np.float64)
+        bad = C.c_uint64(0)
+        _check(lib.brp_stage_resample_compare(self.h, bank, bank.shape[0], C.byref(bad)), "brp_stage_resample_compare")
+        return bad.value
 
     def stage_spectrum(self, count: int | None = None) -> np.ndarray:
         count = self.g.fft_size if count is None else count

@@ -43,8 +43,9 @@ static __constant__ float2 c_brp_sincos[65] = {
 // sin(x) by table + second-order Taylor step, erp_utilities.cpp:184-205:
 //   xt = modff(x/2pi); if (xt < 0) xt += 1;  i0 = (int)(xt*64 + 0.5f);  d = 2pi*(xt - i0/64);  d2 = d*(0.5f*d)
 //   sin = ts + d*tc - d2*ts
+// `cell` receives the table index i0 (0..64) the value was expanded around.
 template <typename Table>
-__device__ __forceinline__ float brp_sin_lut(float x, const Table &tab)
+__device__ __forceinline__ float brp_sin_lut_cell(float x, const Table &tab, int &cell)
 {
     const float y = __fmul_rn(BRP_TWO_PI_INV, x);
     float fr;
@@ -68,7 +69,15 @@ __device__ __forceinline__ float brp_sin_lut(float x, const Table &tab)
     const float d = __fmul_rn(BRP_TWO_PI, __fmaf_rn(i0f, -0.015625f, xt));
     const float d2 = __fmul_rn(d, __fmul_rn(0.5f, d));
     const float2 sc = tab[i0];
+    cell = i0;
     return __fsub_rn(__fadd_rn(sc.x, __fmul_rn(d, sc.y)), __fmul_rn(d2, sc.x));
+}
+
+template <typename Table>
+__device__ __forceinline__ float brp_sin_lut(float x, const Table &tab)
+{
+    int cell;
+    return brp_sin_lut_cell(x, tab, cell);
 }
 
 // del_t for sample index i_f (a float that holds an exact integer), demod_binary_resamp_cpu.c:93-101
@@ -78,6 +87,16 @@ __device__ __forceinline__ float brp_del_t(float i_f, float tau, float Omega, fl
 {
     const float t = __fmul_rn(i_f, dt);
     const float s = brp_sin_lut(__fadd_rn(__fmul_rn(Omega, t), Psi0), tab);
+    return __fsub_rn(__fmul_rn(__fmul_rn(tau, s), step_inv), S0);
+}
+
+// same, also reporting the table cell (used by the run detection of the resampler)
+template <typename Table>
+__device__ __forceinline__ float brp_del_t_cell(float i_f, float tau, float Omega, float Psi0, float S0, float dt,
+                                                float step_inv, const Table &tab, int &cell)
+{
+    const float t = __fmul_rn(i_f, dt);
+    const float s = brp_sin_lut_cell(__fadd_rn(__fmul_rn(Omega, t), Psi0), tab, cell);
     return __fsub_rn(__fmul_rn(__fmul_rn(tau, s), step_inv), S0);
 }
 

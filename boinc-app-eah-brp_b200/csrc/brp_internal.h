@@ -33,9 +33,11 @@ inline uint32_t brp_resamp_blocks(uint32_t nu)
 // out: batch x out_stride floats; [0, n_steps) of each row is written (and [n_steps, n) with the mean when
 // fill_padding).  idx_out (batch x nu int32) optional.  partials: batch x brp_resamp_blocks(nu) doubles;
 // counters: batch uint32, must be zero on entry and are left zero on exit.
+cudaError_t brp_launch_count_mismatch(const int32_t *a, const int32_t *b, uint32_t n, unsigned long long *count, cudaStream_t st);
 cudaError_t brp_launch_resample(const float *series, const BrpTemplateDev *tmpl, int batch, const BrpGeomDev &g,
                                 float *out, size_t out_stride, int32_t *idx_out, uint32_t *n_steps, float *mean,
-                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st);
+                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st,
+                                bool every_sample = false /* skip the run detection: timing model at every sample */);
 cudaError_t brp_launch_sin_lut(const float *x, float *out, uint32_t n, cudaStream_t st);
 cudaError_t brp_launch_round_index(const float *f, int32_t *out, uint32_t n, cudaStream_t st);
 

@@ -16,7 +16,26 @@
 //   * the mean padding (:130-133) is not materialised in batched mode: the FFT's first pass substitutes
 //     mean for i >= n_steps on load.  The legacy entry point asks for it to be written (fill_padding).
 //
-// grid = (ceil(Nu/4096), batch), block = 256.  HBM-bound: 4*Nu read (L2-resident across the batch) +
+// Run detection (MODE 2, the production path).  The shift idx(i) - i changes once per ~1000 samples only, so the
+// timing model is evaluated at every FOURTH sample (one per thread and group of four) and the three samples in
+// between are proven, not computed:
+//   (1) G(i, x) = (int)(fl(i - x) + 0.5) is non-increasing in x (float subtraction and the rounding are monotone), so
+//       lo <= del_t[i] <= hi  and  G(i, lo) == G(i, hi)  pin idx(i) without evaluating del_t[i];
+//   (2) for integer i below 2^23 and i - x inside one binade [2^e, 2^(e+1)), fl(i - x) = i - c(x, e): i is an even
+//       multiple of the binade's spacing, so round-to-nearest-even of i - x does not depend on i.  Hence
+//       G(i, x) - i is the same for every i of the group and is computed once, at the group's first sample;
+//   (3) del_t of the inner samples lies between the values at the two ends of the group, up to rounding: the computed
+//       phase fl(fl(Omega*fl(i*dt)) + Psi0) is monotone in i, so is the expansion variable d while the table cell
+//       does not change, and the table polynomial is monotone in d over a group (at the two cells where its
+//       derivative changes sign the excursion is below 1e-10).  What is not monotone is the rounding of the seven
+//       operations behind d: at most 7e-7 * |tau|*step_inv per value.  eta = 2.5e-6*|tau|*step_inv + 1e-6 covers the
+//       three values involved with room to spare.
+// A group falls back to evaluating all four samples when its ends lie in different table cells, when the two
+// bounds of (1) disagree (a shift change may lie inside), when i - x crosses a binade or is below 1.  The tests
+// compare the index arrays with the oracle bit for bit, and brp_stage_resample_compare() checks MODE 2 against MODE 1
+// sample by sample on the device for whole banks.
+//
+// grid = (ceil(Nu/16384), batch), block = 256, four chunks of 4096 samples per block.  HBM-bound: 4*Nu read (L2-resident across the batch) +
 // 4*n_steps written per template.
 #include "brp_device.cuh"
 #include "brp_internal.h"
@@ -38,6 +57,14 @@ __device__ __forceinline__ int round_index(float f)
     return FAST ? brp_round_index_fast(f) : brp_round_index_exact(f);
 }
 
+constexpr int kGroupLen = BRP_RESAMP_SAMPLES_PER_BLOCK / BRP_RESAMP_THREADS; // 16 samples per timing-model evaluation
+constexpr int kGroups = BRP_RESAMP_THREADS;                                    // groups per chunk of 4096 samples
+static_assert(kGroupLen == 16 && 128 % kGroupLen == 0, "the lane mapping below assumes 16-sample groups");
+// A block walks kChunks chunks: the block-level epilogue (reduction, fence, atomic) is a serial chain of a few
+// microseconds, and with one chunk per block that chain, not bandwidth or issue slots, set the kernel's duration.
+constexpr int kChunks = 4;
+constexpr uint32_t kBlockSpan = (uint32_t)kChunks * BRP_RESAMP_SAMPLES_PER_BLOCK;
+
 __device__ __forceinline__ double warp_sum(double v)
 {
 #pragma unroll
@@ -45,21 +72,25 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-template <bool FAST, bool WRITE_IDX>
+// MODE 0: index by the literal double arithmetic (series longer than 2^22); 1: FP32 index path, every sample
+// evaluated; 2: FP32 index path with run detection.
+template <int MODE, bool WRITE_IDX>
 __global__ void __launch_bounds__(BRP_RESAMP_THREADS)
 resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restrict__ tmpl, BrpGeomDev g,
                 float *__restrict__ out, size_t out_stride, int32_t *__restrict__ idx_out,
                 uint32_t *__restrict__ n_steps_out, float *__restrict__ mean_out, double *__restrict__ partials,
                 uint32_t *__restrict__ counters)
 {
+    constexpr bool FAST = MODE != 0;
     __shared__ float2 s_tab[65];
+    __shared__ float2 s_ends[MODE == 2 ? 2 : 1][MODE == 2 ? kGroups + 1 : 1]; // (del_t, table cell) at the first sample of every group
     __shared__ int s_nsteps;
     __shared__ double s_warp[BRP_RESAMP_THREADS / 32];
     __shared__ bool s_last;
 
     const int b = blockIdx.y;
     const uint32_t nblk = gridDim.x;
-    const uint32_t block_lo = blockIdx.x * BRP_RESAMP_SAMPLES_PER_BLOCK;
+    const uint32_t block_lo = blockIdx.x * kBlockSpan;
     const BrpTemplateDev tp = tmpl[b];
     const uint32_t nu = g.nu;
 
@@ -73,7 +104,7 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
     const uint32_t reach = (uint32_t)(2.02f * fabsf(tp.tau) * g.step_inv) + 16u;
     const uint32_t win_lo = (nu - 1 > reach) ? (nu - 1 - reach) : 0u;
     uint32_t n_steps = nu; // "everything in this block is below n_steps"
-    const bool tail_block = block_lo + BRP_RESAMP_SAMPLES_PER_BLOCK > win_lo;
+    const bool tail_block = block_lo + kBlockSpan > win_lo;
     if (tail_block) {
         const float limit = (float)(nu - 1);
         int best = -1;
@@ -93,15 +124,18 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
 
     // ---- gather: out[i] = series[(int)(i - del_t[i] + 0.5)] for i < n_steps  (demod_binary_resamp_cpu.c:113-121)
     float *const orow = out + (size_t)b * out_stride;
+    int32_t *const irow = WRITE_IDX ? idx_out + (size_t)b * nu : nullptr;
     double acc = 0.0;
     // the packed path needs |Omega*t + Psi0| / 2pi < 2^22 for every sample: true for any physical template
     const bool packed_ok = (fabsf(tp.Omega) * ((float)nu * g.dt) + fabsf(tp.Psi0)) * BRP_TWO_PI_INV < 4.0e6f;
-#pragma unroll
-    for (int it = 0; it < BRP_RESAMP_SAMPLES_PER_BLOCK / (4 * BRP_RESAMP_THREADS); ++it) {
-        const uint32_t i0 = block_lo + (uint32_t)it * (4 * BRP_RESAMP_THREADS) + 4u * threadIdx.x;
-        if (i0 >= n_steps) continue;
-        float v[4];
-        int id[4];
+    // run detection additionally needs a group to span far less than one table cell (1/64 cycle)
+    const float amp = fabsf(tp.tau) * g.step_inv;
+    const bool runs_ok = MODE == 2 && packed_ok && fabsf(tp.Omega) * g.dt * (float)kGroupLen < 0.01f && amp < 4.0e6f;
+    const float eta = 2.5e-6f * amp + 1.0e-6f;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    // four samples i0..i0+3 by the timing model itself
+    auto four_samples = [&](uint32_t i0, float (&v)[4], int (&id)[4]) {
         const float base = (float)i0;
         if (FAST && packed_ok) {
             // two samples per instruction (FADD2/FMUL2/FFMA2), bit-identical to the scalar path
@@ -124,20 +158,97 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
         }
 #pragma unroll
         for (int e = 0; e < 4; ++e) v[e] = __ldg(series + id[e]);
+    };
+    auto emit = [&](uint32_t i0, const float (&v)[4], const int (&id)[4]) {
         if (i0 + 3 < n_steps) {
             *reinterpret_cast<float4 *>(orow + i0) = make_float4(v[0], v[1], v[2], v[3]);
             acc += (double)((v[0] + v[1]) + (v[2] + v[3]));
-            if (WRITE_IDX) *reinterpret_cast<int4 *>(idx_out + (size_t)b * nu + i0) = make_int4(id[0], id[1], id[2], id[3]);
+            if (WRITE_IDX) *reinterpret_cast<int4 *>(irow + i0) = make_int4(id[0], id[1], id[2], id[3]);
         } else {
 #pragma unroll
             for (int e = 0; e < 4; ++e)
                 if (i0 + e < n_steps) {
                     orow[i0 + e] = v[e];
                     acc += (double)v[e];
-                    if (WRITE_IDX) idx_out[(size_t)b * nu + i0 + e] = id[e];
+                    if (WRITE_IDX) irow[i0 + e] = id[e];
                 }
         }
-    }
+    };
+
+#pragma unroll 1
+    for (int chunk = 0; chunk < kChunks; ++chunk) {
+        const uint32_t chunk_lo = block_lo + (uint32_t)chunk * BRP_RESAMP_SAMPLES_PER_BLOCK;
+        if (chunk_lo >= n_steps) break; // uniform
+        // a warp owns 512 consecutive samples of the chunk; in round r lane l handles the four samples at 128 r + 4 l
+        const uint32_t seg_lo = chunk_lo + (uint32_t)warp * (32 * kGroupLen);
+        if (MODE != 2 || !runs_ok) {
+#pragma unroll
+            for (int r = 0; r < kGroupLen / 4; ++r) {
+                const uint32_t i0 = seg_lo + 128u * r + 4u * lane;
+                if (i0 >= n_steps) continue;
+                float v[4];
+                int id[4];
+                four_samples(i0, v, id);
+                emit(i0, v, id);
+            }
+            continue;
+        }
+        if constexpr (MODE == 2) {
+            // one evaluation per group of kGroupLen samples (lane l: group l of the warp's segment)
+            float2(&ends)[kGroups + 1] = s_ends[chunk & 1]; // double-buffered: one barrier per chunk
+            const uint32_t g_lo = seg_lo + (uint32_t)lane * kGroupLen;
+            int cell;
+            const float d_own = brp_del_t_cell((float)g_lo, tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, cell);
+            ends[threadIdx.x] = make_float2(d_own, __int_as_float(cell));
+            if (threadIdx.x == BRP_RESAMP_THREADS - 1) { // right end of the chunk's last group
+                int c2;
+                const float d2 = brp_del_t_cell((float)(g_lo + kGroupLen), tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, c2);
+                ends[kGroups] = make_float2(d2, __int_as_float(c2));
+            }
+            __syncthreads();
+            const float2 eb = ends[threadIdx.x + 1];
+            const float base = (float)g_lo;
+            const float lo = __fsub_rn(fminf(d_own, eb.x), eta), hi = __fadd_rn(fmaxf(d_own, eb.x), eta);
+            const float a = __fsub_rn(base, hi);                                        // smallest i - x of the group
+            const float z = __fsub_rn(__fadd_rn(base, (float)(kGroupLen - 1)), lo);     // largest
+            const int ka = brp_round_index_fast(a), kb = brp_round_index_fast(__fsub_rn(base, lo));
+            const bool proven = cell == __float_as_int(eb.y) && ka == kb && a >= 1.0f &&
+                                ((__float_as_int(a) ^ __float_as_int(z)) & 0x7F800000) == 0;
+            const int verdict = proven ? ka : -1; // index of the group's first sample, or "evaluate every sample"
+#pragma unroll
+            for (int r = 0; r < kGroupLen / 4; ++r) {
+                const int src = r * (128 / kGroupLen) + lane / (kGroupLen / 4);
+                const int first = __shfl_sync(0xffffffffu, verdict, src);
+                const uint32_t i0 = seg_lo + 128u * r + 4u * lane;
+                if (i0 >= n_steps) continue;
+                float v[4];
+                int id[4];
+                if (first >= 0) {
+                    const int k = first + 4 * (lane % (kGroupLen / 4));
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) id[e] = min(k + e, (int)nu - 1);
+                    // four consecutive input samples: two aligned 128-bit loads instead of four scalar ones
+                    const int k4 = k & ~3;
+                    if (k4 + 8 <= (int)nu) {
+                        const float4 *p4 = reinterpret_cast<const float4 *>(series + k4);
+                        const float4 q0 = __ldg(p4), q1 = __ldg(p4 + 1);
+                        switch (k & 3) {
+                        case 0: v[0] = q0.x; v[1] = q0.y; v[2] = q0.z; v[3] = q0.w; break;
+                        case 1: v[0] = q0.y; v[1] = q0.z; v[2] = q0.w; v[3] = q1.x; break;
+                        case 2: v[0] = q0.z; v[1] = q0.w; v[2] = q1.x; v[3] = q1.y; break;
+                        default: v[0] = q0.w; v[1] = q1.x; v[2] = q1.y; v[3] = q1.z; break;
+                        }
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) v[e] = __ldg(series + id[e]);
+                    }
+                } else {
+                    four_samples(i0, v, id);
+                }
+                emit(i0, v, id);
+            }
+        }
+    } // chunks
 
     // ---- mean: fixed-order block reduction, per-block partials, last block of the template finishes
     acc = warp_sum(acc);
@@ -195,25 +306,45 @@ __global__ void round_index_kernel(const float *__restrict__ f, int32_t *__restr
     out[i] = (v < 8388608.0f) ? brp_round_index_fast(v) : brp_round_index_exact(v);
 }
 
+__global__ void count_mismatch_kernel(const int32_t *__restrict__ a, const int32_t *__restrict__ b, uint32_t n,
+                                      unsigned long long *__restrict__ count)
+{
+    unsigned int bad = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) bad += a[i] != b[i];
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(count, (unsigned long long)bad);
+}
+
 } // namespace
+
+cudaError_t brp_launch_count_mismatch(const int32_t *a, const int32_t *b, uint32_t n, unsigned long long *count, cudaStream_t st)
+{
+    count_mismatch_kernel<<<296, 256, 0, st>>>(a, b, n, count);
+    return cudaGetLastError();
+}
 
 cudaError_t brp_launch_resample(const float *series, const BrpTemplateDev *tmpl, int batch, const BrpGeomDev &g,
                                 float *out, size_t out_stride, int32_t *idx_out, uint32_t *n_steps, float *mean,
-                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st)
+                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st, bool every_sample)
 {
-    const dim3 grid(brp_resamp_blocks(g.nu), batch);
+    const dim3 grid((g.nu + kBlockSpan - 1) / kBlockSpan, batch);
     // the FP32 index path needs every i - del_t below 2^23; |del_t| is far below 2^22 for any sane template
     const bool fast = g.nu <= (1u << 22);
-    if (fast) {
+    if (fast && !every_sample) {
         if (idx_out)
-            resample_kernel<true, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<2, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
         else
-            resample_kernel<true, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<2, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+    } else if (fast) {
+        if (idx_out)
+            resample_kernel<1, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+        else
+            resample_kernel<1, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
     } else {
         if (idx_out)
-            resample_kernel<false, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<0, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
         else
-            resample_kernel<false, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<0, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;

@@ -427,6 +427,55 @@ int brp_stage_resample(brp_search *s, const brp_template *t, float *resampled_ou
     return 0;
 }
 
+int brp_stage_resample_compare(brp_search *s, const double *bank, uint32_t n_templates, uint64_t *n_mismatch)
+{
+    if (!s || !bank || !n_mismatch) return RADPUL_EVAL;
+    CU_TRY(cudaSetDevice(s->device), RADPUL_CUDA_DEVICE_SET);
+    int rc = ensure_templates(s, 1);
+    if (rc) return rc;
+    const size_t nfull = ((size_t)s->g.nsamples + 3) & ~(size_t)3;
+    const uint32_t nu = s->g.nsamples_unpadded;
+    if (!s->d_tap_series) CU_TRY(cudaMalloc((void **)&s->d_tap_series, sizeof(float) * nfull), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    if (!s->d_tap_idx) CU_TRY(cudaMalloc((void **)&s->d_tap_idx, sizeof(int32_t) * s->rs_stride), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    int32_t *d_idx2 = NULL;
+    unsigned long long *d_count = NULL;
+    uint32_t *d_ns2 = NULL;
+    CU_TRY(cudaMalloc((void **)&d_idx2, sizeof(int32_t) * s->rs_stride), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    if (cudaMalloc((void **)&d_count, 8) != cudaSuccess || cudaMalloc((void **)&d_ns2, 8) != cudaSuccess) {
+        cudaFree(d_idx2);
+        cudaFree(d_count);
+        return RADPUL_CUDA_MEM_ALLOC_DEVICE;
+    }
+    cudaError_t e = cudaMemsetAsync(d_count, 0, 8, s->stream);
+    for (uint32_t t = 0; t < n_templates && e == cudaSuccess; t++) {
+        brp_template bt;
+        brp_derive_template(bank[3 * t], bank[3 * t + 1], bank[3 * t + 2], s->g.step_inv, &bt);
+        cudaStreamSynchronize(s->stream); // h_tmpl is reused
+        s->h_tmpl[0].tau = bt.tau; s->h_tmpl[0].Omega = bt.Omega; s->h_tmpl[0].Psi0 = bt.Psi0; s->h_tmpl[0].S0 = bt.S0;
+        e = cudaMemcpyAsync(s->d_tmpl, s->h_tmpl, sizeof(BrpTemplateDev), cudaMemcpyHostToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(s->d_tap_idx, 0xFF, sizeof(int32_t) * nu, s->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(d_idx2, 0xFF, sizeof(int32_t) * nu, s->stream);
+        if (e == cudaSuccess)
+            e = brp_launch_resample(s->d_series, s->d_tmpl, 1, s->gd, s->d_tap_series, nfull, s->d_tap_idx, s->d_nsteps, s->d_mean,
+                                    s->d_partials, s->d_counters, false, s->stream, false);
+        if (e == cudaSuccess)
+            e = brp_launch_resample(s->d_series, s->d_tmpl, 1, s->gd, s->d_tap_series, nfull, d_idx2, d_ns2, s->d_mean,
+                                    s->d_partials, s->d_counters, false, s->stream, true);
+        if (e == cudaSuccess) e = brp_launch_count_mismatch(s->d_tap_idx, d_idx2, nu, d_count, s->stream);
+        if (e == cudaSuccess) e = brp_launch_count_mismatch((const int32_t *)s->d_nsteps, (const int32_t *)d_ns2, 1, d_count, s->stream);
+        s->launches += 4;
+    }
+    unsigned long long h = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h, d_count, 8, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    cudaFree(d_idx2);
+    cudaFree(d_count);
+    cudaFree(d_ns2);
+    if (e != cudaSuccess) return RADPUL_CUDA_KERNEL_INVOKE;
+    *n_mismatch = h;
+    return 0;
+}
+
 static int spectrum_common(brp_search *s, const float *d_in, size_t in_stride, float *ps_out, uint32_t count)
 {
     if (count > s->g.fft_size) return RADPUL_EVAL;

@@ -231,6 +231,10 @@ int brp_search_profile_batch(brp_search *s, const double *bank, uint32_t batch, 
  * index_out: Nu int32 (entries >= n_steps untouched) */
 int brp_stage_resample(brp_search *s, const brp_template *t, float *resampled_out, int32_t *index_out,
                        uint32_t *n_steps_out, float *mean_out);
+/* For every template of bank[0..n): resample with the production kernel (timing model evaluated at every fourth sample,
+ * the samples in between proven from the two ends) and with the timing model evaluated at every sample, and count the
+ * positions where the two index arrays (or n_steps) differ.  Must be 0; runs wholly on the device. */
+int brp_stage_resample_compare(brp_search *s, const double *bank, uint32_t n_templates, uint64_t *n_mismatch);
 /* spectrum of the series resampled last by brp_stage_resample: ps_out[0..count), count <= F */
 int brp_stage_spectrum(brp_search *s, float *ps_out, uint32_t count);
 /* spectrum of an arbitrary HOST series of N floats (n_steps = N, no padding): FFT kernels alone */

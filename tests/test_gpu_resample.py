@@ -78,3 +78,42 @@ def test_resample_unaligned_length_and_dc_offset(oracle):
         exact = float(np.mean(series[idx[:ns]].astype(np.float64)))
         assert abs(mean - exact) <= 2e-7 * abs(exact)
     s.close()
+
+
+ADVERSARIAL = np.array([
+    [1000.0, 0.0, 0.0],          # null template: del_t == 0 everywhere
+    [660.0, 0.335, 6.2],         # corner of the production bank
+    [120.0, 1.0, 1.0],           # amplitude 15 000 samples, 2.3 orbits per work-unit
+    [40.0, 3.0, 5.5],            # amplitude 46 000 samples, slope 0.47 samples/sample
+    [11.0, 0.8, 0.1],            # 25 orbits: many table-cell and cycle boundaries
+    [2.0, 0.05, 2.0],            # a table cell lasts ~480 samples
+    [0.3, 0.01, 4.0],            # a table cell lasts ~70 samples
+    [900.0, -0.3, 3.0],          # negative amplitude
+    [1500.0, 0.33, -40.0],       # negative phase, several cycles
+    [1e6, 0.335, 1.0],           # a fraction of one table cell in the whole work-unit
+])
+
+
+@pytest.mark.parametrize("log2n", [16, 20, 22])
+def test_run_detection_equals_per_sample_evaluation(oracle, log2n):
+    """The production resampler evaluates the timing model at every fourth sample and proves the indices in between
+    (csrc/resamp.cu, "Run detection").  Against the same kernel evaluating every sample, on the device, whole banks at a
+    time: not one index may differ.  The per-sample path is itself pinned to the oracle above and, for the adversarial
+    orbits, here."""
+    nu = 1 << log2n
+    series, _ = synth.make_series(nu, seed=7, pulsar=None)
+    g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, 1.0, 400.0, 1000)
+    s = brp_b200.Search(g, max_batch=1)
+    s.set_series(series)
+    n_bank = 6662 if log2n == 22 else 1500
+    assert s.stage_resample_compare(synth.make_bank(n_bank)) == 0
+    assert s.stage_resample_compare(small_bank(300, seed=3)) == 0
+    assert s.stage_resample_compare(ADVERSARIAL) == 0
+    if log2n <= 20:
+        go = oracle.geometry(nu, synth.TSAMPLE_US, 1.0, 400.0, 1000)
+        for row in ADVERSARIAL:
+            t = brp_b200.derive_template(*row, g.step_inv)
+            _, idx, ns, _ = oracle.resample(series, go, oracle.template(*row, go.step_inv))
+            _, gidx, gns, _ = s.stage_resample(t, want_series=False)
+            assert gns == ns and np.array_equal(gidx[:ns], idx[:ns]), row
+    s.close()
