@@ -88,6 +88,65 @@ __device__ __forceinline__ void issue_tile(const float *__restrict__ ps, size_t 
                      : "memory");
 }
 
+template <int IMM>
+__device__ __forceinline__ float lds_at(uint32_t a)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(a), "n"(IMM));
+    return v;
+}
+
+// the five sums of bin iu = i + U*256 of the tile in ring stage ST, and the rare path if any beats its threshold
+template <int ST, int U>
+__device__ __forceinline__ void sum_bin(const uint32_t (&addr)[17], uint32_t i, const BrpGeomDev &g, const BrpThresholds &thr,
+                                        uint32_t tkey, unsigned long long *__restrict__ keys)
+{
+    const uint32_t iu = i + U * kHsThreads;
+#define PH(l) lds_at<4 * (ST * kSmemFloats + U * ((l) * kHsThreads / 16))>(addr[l])
+    const float s0 = PH(16);
+    const float s1 = s0 + PH(8);
+    const float s2 = s1 + (PH(12) + PH(4));
+    const float s3 = s2 + (((PH(14) + PH(10)) + PH(6)) + PH(2));
+    const float s4 = s3 + (((((((PH(15) + PH(13)) + PH(11)) + PH(9)) + PH(7)) + PH(5)) + PH(3)) + PH(1));
+#undef PH
+    const bool any = (s0 > thr.t[0]) | (s1 > thr.t[1]) | (s2 > thr.t[2]) | (s3 > thr.t[3]) | (s4 > thr.t[4]);
+    // bins outside [w2, H) only exist in the first and last tile of a template (their slots may hold stale data)
+    if (any && iu >= g.w2 && iu < g.h) record_hits(iu, s0, s1, s2, s3, s4, thr, g.fu, tkey, keys);
+}
+
+// sum the tile staged in ring stage ST (after issuing the copies of the CTA's next tile into the other stage)
+template <int ST>
+__device__ __forceinline__ void sum_tile(const float *__restrict__ ps, size_t ps_stride, const BrpGeomDev &g, const BrpThresholds &thr,
+                                         uint32_t first_template, uint32_t tile0, uint32_t tiles_per_template, uint32_t total_tiles,
+                                         unsigned long long *__restrict__ keys, float *sm, uint32_t bar0, const uint32_t (&addr)[17],
+                                         uint32_t tile, uint32_t n)
+{
+    const uint32_t next = tile + gridDim.x;
+    // the other stage was fully consumed before the __syncthreads that ended the previous tile
+    if (next < total_tiles && threadIdx.x < 32)
+        issue_tile(ps, ps_stride, g, tile0, next, tiles_per_template, sm + (ST ^ 1) * kSmemFloats, bar0 + 8 * (ST ^ 1));
+
+    const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
+    const uint32_t tkey = 0xFFFFFFFFu - (first_template + b);
+    const uint32_t i = (tile0 + bx) * kSpan + threadIdx.x;
+    {   // wait for this stage's copies: use number n>>1 of the barrier -> parity (n>>1)&1
+        const uint32_t parity = (n >> 1) & 1u, baddr = bar0 + 8 * ST;
+        uint32_t done = 0;
+        while (!done) {
+            asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                         : "=r"(done)
+                         : "r"(baddr), "r"(parity)
+                         : "memory");
+        }
+    }
+    static_assert(kHsPerThread == 4, "unrolled by hand");
+    sum_bin<ST, 0>(addr, i, g, thr, tkey, keys);
+    sum_bin<ST, 1>(addr, i, g, thr, tkey, keys);
+    sum_bin<ST, 2>(addr, i, g, thr, tkey, keys);
+    sum_bin<ST, 3>(addr, i, g, thr, tkey, keys);
+    __syncthreads(); // everyone is done with stage ST before it is refilled two tiles later
+}
+
 // Persistent CTAs: each loops over tiles (kSpan bins of one template) with a two-deep shared-memory ring, so the
 // bulk copies of the next tile run while the current one is summed.
 __global__ void __launch_bounds__(kHsThreads)
@@ -109,47 +168,18 @@ harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomD
     if (tile < total_tiles && threadIdx.x < 32) issue_tile(ps, ps_stride, g, tile0, tile, tiles_per_template, sm, bar0);
 
     // Tiles are aligned to kSpan, so bin i0 + t + 256 u of harmonic l sits at slice offset ((l t + 8) >> 4) + 16 l u:
-    // the first term is a per-thread constant for the whole kernel, the second an immediate.
-    uint32_t off[17];
+    // the first term is a per-thread constant for the whole kernel (kept as a shared-memory byte address), the second
+    // and the ring stage are immediates of the load instruction (the tile loop is unrolled over the two stages).
+    uint32_t addr[17];
 #pragma unroll
-    for (int l = 1; l <= 16; ++l) off[l] = slice_off(l) + (((uint32_t)l * threadIdx.x + 8u) >> 4);
+    for (int l = 1; l <= 16; ++l) addr[l] = smem_u32(sm) + 4u * (slice_off(l) + (((uint32_t)l * threadIdx.x + 8u) >> 4));
 
-    for (uint32_t n = 0; tile < total_tiles; tile += gridDim.x, ++n) {
-        const uint32_t st = n & 1u;
-        const uint32_t next = tile + gridDim.x;
-        // the other stage was fully consumed before the __syncthreads that ended the previous iteration
-        if (next < total_tiles && threadIdx.x < 32)
-            issue_tile(ps, ps_stride, g, tile0, next, tiles_per_template, sm + (st ^ 1u) * kSmemFloats, bar0 + 8 * (st ^ 1u));
-
-        const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
-        const uint32_t tkey = 0xFFFFFFFFu - (first_template + b);
-        const uint32_t i = (tile0 + bx) * kSpan + threadIdx.x;
-        const float *__restrict__ buf = sm + st * kSmemFloats;
-        {   // wait for this stage's copies: use number n>>1 of the barrier -> parity (n>>1)&1
-            const uint32_t parity = (n >> 1) & 1u, addr = bar0 + 8 * st;
-            uint32_t done = 0;
-            while (!done) {
-                asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-                             : "=r"(done)
-                             : "r"(addr), "r"(parity)
-                             : "memory");
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < kHsPerThread; ++u) {
-            const uint32_t iu = i + u * kHsThreads;
-#define PH(l) buf[off[l] + u * ((l) * kHsThreads / 16)]
-            const float s0 = PH(16);
-            const float s1 = s0 + PH(8);
-            const float s2 = s1 + (PH(12) + PH(4));
-            const float s3 = s2 + (((PH(14) + PH(10)) + PH(6)) + PH(2));
-            const float s4 = s3 + (((((((PH(15) + PH(13)) + PH(11)) + PH(9)) + PH(7)) + PH(5)) + PH(3)) + PH(1));
-#undef PH
-            const bool any = (s0 > thr.t[0]) | (s1 > thr.t[1]) | (s2 > thr.t[2]) | (s3 > thr.t[3]) | (s4 > thr.t[4]);
-            // bins outside [w2, H) only exist in the first and last tile of a template (their slots may hold stale data)
-            if (any && iu >= g.w2 && iu < g.h) record_hits(iu, s0, s1, s2, s3, s4, thr, g.fu, tkey, keys);
-        }
-        __syncthreads(); // everyone is done with stage `st` before it is refilled two iterations later
+    for (uint32_t n = 0; tile < total_tiles; n += 2) {
+        sum_tile<0>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total_tiles, keys, sm, bar0, addr, tile, n);
+        tile += gridDim.x;
+        if (tile >= total_tiles) break;
+        sum_tile<1>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total_tiles, keys, sm, bar0, addr, tile, n + 1);
+        tile += gridDim.x;
     }
 }
 
