@@ -24,6 +24,8 @@ NVCC_FLAGS = [
 
 
 PER_SOURCE_FLAGS: dict[str, list[str]] = {}
+# tuning experiments: BRP_EXTRA_NVCC_FLAGS="-DBRP_HS_STAGES=3" python build.py --force
+EXTRA_FLAGS = os.environ.get("BRP_EXTRA_NVCC_FLAGS", "").split()
 
 
 def _stale(out: Path, deps: list[Path]) -> bool:
@@ -43,7 +45,7 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
         obj = objdir / (src.rsplit(".", 1)[0] + ".o")
         objs.append(obj)
         if force or _stale(obj, [CSRC / src] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + PER_SOURCE_FLAGS.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu", "-c", str(CSRC / src), "-o", str(obj)]
+            cmd = [nvcc] + NVCC_FLAGS + EXTRA_FLAGS + PER_SOURCE_FLAGS.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu", "-c", str(CSRC / src), "-o", str(obj)]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for src, p in procs:

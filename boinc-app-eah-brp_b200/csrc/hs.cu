@@ -22,9 +22,13 @@
 // slice of the spectrum, P[(l*i0+8)>>4 .. (l*i1+8)>>4] (l*kSpan/16 + 1 floats), so the sixteen slices are
 // brought into shared memory by sixteen 1-D bulk async copies (TMA, cp.async.bulk + mbarrier): no load
 // instructions, no registers, no L1 wavefronts on the way in.  CTAs are persistent and walk the tiles of the
-// whole batch with a two-deep ring: warp 0 issues the copies of tile t+1 while all warps sum tile t.
-// Because i0 is a multiple of 1024, (l*i0+8)>>4 = l*i0/16 exactly, and the position of bin i0+tid+256*r inside
-// slice l is ((l*tid+8)>>4) + 16*l*r: a per-thread constant plus a compile-time offset.  The hot loop therefore
+// whole batch with a two-deep ring; a producer warp issues the copies of tile t+1 while four consumer warps sum
+// tile t (eight bins per thread), stages handed over through full/empty mbarriers without any block-wide barrier.
+// Measured on B200 (tools/hs_sweep.sh): 2 stages x 1024 bins x 4 consumer warps, three CTAs per SM, is the fastest
+// shape (77 us per 16 templates = 12.4 TB/s out of L2, the L2 -> SM limit); deeper rings or wider CTAs lose more
+// to the lower CTA count than they gain in prefetch distance.
+// Because i0 is a multiple of 1024, (l*i0+8)>>4 = l*i0/16 exactly, and the position of bin i0+tid+128*r inside
+// slice l is ((l*tid+8)>>4) + 8*l*r: a per-thread constant plus a compile-time offset.  The hot loop therefore
 // has no index arithmetic at all; consecutive lanes read consecutive or identical shared-memory words
 // (conflict-free, broadcast).
 // Algorithmic traffic 4*H bytes per template; the slices of different harmonics overlap in the spectrum,
@@ -33,8 +37,18 @@
 
 namespace {
 
-constexpr int kHsThreads = 256;
-constexpr int kHsPerThread = 4;                       // bins per thread, kHsThreads apart
+#ifndef BRP_HS_THREADS
+#define BRP_HS_THREADS 128
+#endif
+constexpr int kHsThreads = BRP_HS_THREADS;  // consumer threads (one more warp issues the copies)
+#ifndef BRP_HS_PER_THREAD
+#define BRP_HS_PER_THREAD 8
+#endif
+#ifndef BRP_HS_STAGES
+#define BRP_HS_STAGES 2
+#endif
+constexpr int kHsPerThread = BRP_HS_PER_THREAD;       // bins per thread, kHsThreads apart
+constexpr int kStages = BRP_HS_STAGES;                // depth of the shared-memory ring (kStages - 1 tiles in flight)
 constexpr int kSpan = kHsThreads * kHsPerThread;      // bins per tile; tiles start at multiples of kSpan
 // slice l of an aligned tile holds l*kSpan/16 + 1 floats, rounded up to whole 16-byte units
 __host__ __device__ constexpr int slice_cap(int l) { return ((l * kSpan / 16 + 1 + 3) / 4) * 4; }
@@ -114,73 +128,95 @@ __device__ __forceinline__ void sum_bin(const uint32_t (&addr)[17], uint32_t i, 
     if (any && iu >= g.w2 && iu < g.h) record_hits(iu, s0, s1, s2, s3, s4, thr, g.fu, tkey, keys);
 }
 
-// sum the tile staged in ring stage ST (after issuing the copies of the CTA's next tile into the other stage)
-template <int ST>
-__device__ __forceinline__ void sum_tile(const float *__restrict__ ps, size_t ps_stride, const BrpGeomDev &g, const BrpThresholds &thr,
-                                         uint32_t first_template, uint32_t tile0, uint32_t tiles_per_template, uint32_t total_tiles,
-                                         unsigned long long *__restrict__ keys, float *sm, uint32_t bar0, const uint32_t (&addr)[17],
-                                         uint32_t tile, uint32_t n)
+__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity)
 {
-    const uint32_t next = tile + gridDim.x;
-    // the other stage was fully consumed before the __syncthreads that ended the previous tile
-    if (next < total_tiles && threadIdx.x < 32)
-        issue_tile(ps, ps_stride, g, tile0, next, tiles_per_template, sm + (ST ^ 1) * kSmemFloats, bar0 + 8 * (ST ^ 1));
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done)
+                     : "r"(addr), "r"(parity)
+                     : "memory");
+    }
+}
 
+template <int ST, int U>
+__device__ __forceinline__ void sum_bins(const uint32_t (&addr)[17], uint32_t i, const BrpGeomDev &g, const BrpThresholds &thr,
+                                         uint32_t tkey, unsigned long long *__restrict__ keys)
+{
+    if constexpr (U < kHsPerThread) {
+        sum_bin<ST, U>(addr, i, g, thr, tkey, keys);
+        sum_bins<ST, U + 1>(addr, i, g, thr, tkey, keys);
+    }
+}
+
+// consumer side of one tile: wait until ring stage ST is full, sum the thread's bins, hand the stage back
+template <int ST>
+__device__ __forceinline__ void sum_tile(const BrpGeomDev &g, const BrpThresholds &thr, uint32_t first_template, uint32_t tile0,
+                                         uint32_t tiles_per_template, unsigned long long *__restrict__ keys, uint32_t full0,
+                                         uint32_t empty0, const uint32_t (&addr)[17], uint32_t tile, uint32_t n)
+{
     const uint32_t b = tile / tiles_per_template, bx = tile - b * tiles_per_template;
     const uint32_t tkey = 0xFFFFFFFFu - (first_template + b);
     const uint32_t i = (tile0 + bx) * kSpan + threadIdx.x;
-    {   // wait for this stage's copies: use number n>>1 of the barrier -> parity (n>>1)&1
-        const uint32_t parity = (n >> 1) & 1u, baddr = bar0 + 8 * ST;
-        uint32_t done = 0;
-        while (!done) {
-            asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-                         : "=r"(done)
-                         : "r"(baddr), "r"(parity)
-                         : "memory");
-        }
-    }
-    static_assert(kHsPerThread == 4, "unrolled by hand");
-    sum_bin<ST, 0>(addr, i, g, thr, tkey, keys);
-    sum_bin<ST, 1>(addr, i, g, thr, tkey, keys);
-    sum_bin<ST, 2>(addr, i, g, thr, tkey, keys);
-    sum_bin<ST, 3>(addr, i, g, thr, tkey, keys);
-    __syncthreads(); // everyone is done with stage ST before it is refilled two tiles later
+    mbar_wait(full0 + 8 * ST, (n / kStages) & 1u); // use number n / kStages of this stage
+    sum_bins<ST, 0>(addr, i, g, thr, tkey, keys);
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * ST) : "memory");
 }
 
-// Persistent CTAs: each loops over tiles (kSpan bins of one template) with a two-deep shared-memory ring, so the
-// bulk copies of the next tile run while the current one is summed.
-__global__ void __launch_bounds__(kHsThreads)
+// Persistent CTAs, warp-specialised: the last warp only issues the bulk copies (tile n into ring stage n % kStages, as
+// soon as the consumer warps have handed that stage back), the other warps only sum.  Stages are passed through full/empty
+// mbarriers, so there is no block-wide barrier in the loop and a consumer warp never waits for a slower sibling.
+__global__ void __launch_bounds__(kHsThreads + 32)
 harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomDev g, BrpThresholds thr,
                         uint32_t first_template, uint32_t tile0, uint32_t tiles_per_template, uint32_t total_tiles,
                         unsigned long long *__restrict__ keys)
 {
     extern __shared__ __align__(128) float sm[];
-    __shared__ __align__(8) unsigned long long bar[2];
+    __shared__ __align__(8) unsigned long long bar[2 * kStages];
 
-    const uint32_t bar0 = smem_u32(&bar[0]);
+    const uint32_t full0 = smem_u32(&bar[0]), empty0 = smem_u32(&bar[kStages]);
     if (threadIdx.x == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8));
+        for (int q = 0; q < kStages; ++q) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full0 + 8 * q));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty0 + 8 * q), "r"(kHsThreads / 32));
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     uint32_t tile = blockIdx.x;
-    if (tile < total_tiles && threadIdx.x < 32) issue_tile(ps, ps_stride, g, tile0, tile, tiles_per_template, sm, bar0);
 
-    // Tiles are aligned to kSpan, so bin i0 + t + 256 u of harmonic l sits at slice offset ((l t + 8) >> 4) + 16 l u:
+    if (threadIdx.x >= kHsThreads) { // producer warp
+        for (uint32_t n = 0; tile < total_tiles; ++n, tile += gridDim.x) {
+            const uint32_t st = n % kStages;
+            if (n >= kStages) mbar_wait(empty0 + 8 * st, (n / kStages - 1u) & 1u);
+            issue_tile(ps, ps_stride, g, tile0, tile, tiles_per_template, sm + st * kSmemFloats, full0 + 8 * st);
+        }
+        return;
+    }
+
+    // Tiles are aligned to kSpan, so bin i0 + t + 128 u of harmonic l sits at slice offset ((l t + 8) >> 4) + 8 l u:
     // the first term is a per-thread constant for the whole kernel (kept as a shared-memory byte address), the second
-    // and the ring stage are immediates of the load instruction (the tile loop is unrolled over the two stages).
+    // and the ring stage are immediates of the load instruction (the tile loop is unrolled over the ring stages).
     uint32_t addr[17];
 #pragma unroll
     for (int l = 1; l <= 16; ++l) addr[l] = smem_u32(sm) + 4u * (slice_off(l) + (((uint32_t)l * threadIdx.x + 8u) >> 4));
 
-    for (uint32_t n = 0; tile < total_tiles; n += 2) {
-        sum_tile<0>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total_tiles, keys, sm, bar0, addr, tile, n);
-        tile += gridDim.x;
-        if (tile >= total_tiles) break;
-        sum_tile<1>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total_tiles, keys, sm, bar0, addr, tile, n + 1);
-        tile += gridDim.x;
+#define BRP_HS_STEP(ST)                                                                                                         \
+    if constexpr (ST < kStages) {                                                                                               \
+        if (tile >= total_tiles) break;                                                                                         \
+        sum_tile<ST>(g, thr, first_template, tile0, tiles_per_template, keys, full0, empty0, addr, tile, n + ST);               \
+        tile += gridDim.x;                                                                                                      \
     }
+    for (uint32_t n = 0;; n += kStages) {
+        BRP_HS_STEP(0)
+        BRP_HS_STEP(1)
+        BRP_HS_STEP(2)
+        BRP_HS_STEP(3)
+        BRP_HS_STEP(4)
+        BRP_HS_STEP(5)
+    }
+#undef BRP_HS_STEP
 }
 
 __global__ void collect_kernel(const unsigned long long *__restrict__ keys, uint32_t fu, uint32_t w2,
@@ -212,7 +248,7 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
 {
     if (g.h <= g.w2 || batch <= 0) return cudaSuccess;
     static int ctas_per_device[64]; // persistent grid size, per device (0 = not configured yet)
-    const int smem = 2 * kSmemFloats * (int)sizeof(float);
+    const int smem = kStages * kSmemFloats * (int)sizeof(float);
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
@@ -222,7 +258,7 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
         cudaFuncSetAttribute((const void *)harmonic_summing_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         int sms = 0, per_sm = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, harmonic_summing_kernel, kHsThreads, smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, harmonic_summing_kernel, kHsThreads + 32, smem);
         if (e != cudaSuccess) return e;
         ctas_per_device[dev] = (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1); // one resident wave
     }
@@ -231,7 +267,7 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
     const uint32_t tiles_per_template = (g.h + kSpan - 1) / kSpan - tile0;
     const uint32_t total = tiles_per_template * (uint32_t)batch;
     const uint32_t grid = total < (uint32_t)ctas_per_device[dev] ? total : (uint32_t)ctas_per_device[dev];
-    harmonic_summing_kernel<<<grid, kHsThreads, smem, st>>>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total, keys);
+    harmonic_summing_kernel<<<grid, kHsThreads + 32, smem, st>>>(ps, ps_stride, g, thr, first_template, tile0, tiles_per_template, total, keys);
     return cudaGetLastError();
 }
 
