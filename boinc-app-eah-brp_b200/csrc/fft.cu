@@ -32,6 +32,8 @@
 
 #include <vector>
 
+#include <cuda.h> // CUtensorMap (types only; the encoder is looked up at run time, libcuda is not linked)
+
 #include "brp_internal.h"
 
 namespace {
@@ -94,11 +96,11 @@ struct Layout {
     // the radix-32 plans (L = 1024: 32x32, L = 512: 32x16) pad every 32 (resp. 16) positions
     static constexpr int C4 = (L == 1024 || (L == 512 && PASS == 1)) ? 0 : 1;
     static constexpr int C5 = (L == 1024) ? 1 : 0;
-    static constexpr int C8 = (PASS == 2 && (L == 2048 || L == 4096)) ? 1 : 0;
-    static constexpr int EXTRA = PASS == 2 ? (L == 2048 ? (ROWS == 8 ? 2 : 4) : L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
+    static constexpr int C8 = ((PASS == 2 && (L == 2048 || L == 4096)) || PASS == 3) ? 1 : 0; // PASS 3: pass 1 through TMA, see below
+    static constexpr int EXTRA = PASS == 3 ? 2 : PASS == 2 ? (L == 2048 ? (ROWS == 8 ? 2 : 4) : L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
                                            : (L == 1024 ? 2 : ROWS == 4 ? (L % 3 == 0 ? 1 : 2) : ROWS == 2 ? (L == 4096 ? 8 : 4) : 1);
     // permute the low four bits of the butterfly index in the first (global -> shared) stage of pass 1
-    static constexpr bool ROT0 = PASS == 1 && L != 1024 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
+    static constexpr bool ROT0 = PASS != 2 && L != 1024 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
     __host__ __device__ static constexpr int phys(int pos) { return pos + C4 * (pos >> 4) + C5 * (pos >> 5) + C8 * (pos >> 8); }
     static constexpr int PITCH = phys(L) + EXTRA;
     static constexpr int BYTES = ROWS * PITCH * 8;
@@ -109,7 +111,11 @@ __host__ __device__ constexpr int cfg_rows(int L)
     return tile / L < 2 ? 2 : tile / L;
 }
 
-__host__ __device__ constexpr int cfg_threads(int L) { return cfg_rows(L) * L >= 16384 ? 512 : 256; }
+#ifndef BRP_FFT_WIDE_L
+#define BRP_FFT_WIDE_L 2048 // tile length that runs with 512 threads (one butterfly per thread and stage), two CTAs per SM
+#endif
+__host__ __device__ constexpr int cfg_threads(int L) { return (cfg_rows(L) * L >= 16384 || L == BRP_FFT_WIDE_L) ? 512 : 256; }
+__host__ __device__ constexpr int cfg_ctas(int L) { return cfg_rows(L) * L >= 16384 ? 1 : 2; }
 
 // ------------------------------------------------------------------ complex helpers
 // Blackwell packed FP32x2 arithmetic (FADD2 / FFMA2): one instruction per complex add or subtract
@@ -229,7 +235,7 @@ enum { MAP_ROW_FAST = 0, MAP_BF_FAST = 1 };
 //     auto c = io.begin(row, base);   io.get(c, off);   io.put(c, off, q, value);
 // where base = blk*n + p is the butterfly's first position and off = j*S is a compile-time constant after
 // unrolling, so all per-element address arithmetic folds into immediates.
-template <int L, int ROWS, int STAGE, int MAP, bool ROT, typename Load, typename Store>
+template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, typename Load, typename Store>
 __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store)
 {
     constexpr int R = cfg_radix(L, STAGE);
@@ -260,6 +266,10 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
         const auto lc = load.begin(row, base);
 #pragma unroll
         for (int j = 0; j < R; ++j) v[j] = load.get(lc, j * S);
+        if constexpr (SYNC_AFTER_LOAD) { // the store region overlaps the load region: everybody reads before anybody writes
+            static_assert(ITEMS == NT, "one butterfly per thread");
+            __syncthreads();
+        }
         Dft<R>::run(v);
         const auto sc = store.begin(row, base);
         const float2 *__restrict__ twp = tw + TWO + p;
@@ -391,7 +401,7 @@ struct Pass1Store {
 };
 
 template <int L, int ROWS>
-__global__ void __launch_bounds__(cfg_threads(L), cfg_threads(L) == 512 ? 1 : 2)
+__global__ void __launch_bounds__(cfg_threads(L), cfg_ctas(L))
 fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t *__restrict__ n_steps_arr,
                  const float *__restrict__ mean_arr, float2 *__restrict__ work, uint32_t m1, uint32_t m,
                  const float2 *__restrict__ tw, const float2 *__restrict__ tb)
@@ -411,6 +421,137 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
         __syncthreads();
         tile_middle<L, ROWS, 1, 1, NS - 1>(tw, sm);
         tile_stage<L, ROWS, NS - 1, MAP_ROW_FAST, false>(tw, io, gstore);
+    }
+}
+
+// ------------------------------------------------------------------ pass 1 with TMA tensor copies (production shape)
+// A pass-1 tile is 2048 rows of 4 complex columns: 32-byte runs, 8 KB apart.  Moved by per-lane loads and stores every
+// run costs one L1 tag lookup, and those lookups (19 M of the kernel's 28 M L1 wavefronts per launch) set the speed of
+// the plain kernel above.  Here the tile is fetched by eight cp.async.bulk.tensor boxes (256 rows x 32 bytes) that land
+// DENSE in shared memory ([row][column]) without passing through the LSU, stage 0 reads it from there, and the last
+// stage puts its results back in the same dense form for eight tensor stores.  The dense image and the padded
+// exchange layout share the same shared memory, so stage 0 and the last stage read everything before anybody writes.
+// Lane mappings and padding chosen with tools/pass1_tma_layout.py (all accesses conflict-free except the dense read).
+// Arithmetic is the same as in fft_pass1_kernel (same butterflies, same twiddle construction): results are bit-identical.
+constexpr int kTmaL = 2048, kTmaRows = 4, kTmaBox = 256;
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+struct TmaDenseLoad {
+    const float2 *dense;
+    uint32_t m1, col0, n_steps;
+    float mean;
+    struct Ctx {
+        const float2 *p;
+        uint32_t i0;
+        bool fast;
+    };
+    __device__ __forceinline__ Ctx begin(int row, int base) const
+    {
+        constexpr int R = cfg_radix(kTmaL, 0), S = cfg_stride(kTmaL, 0);
+        Ctx c;
+        c.p = dense + base * kTmaRows + row;
+        c.i0 = 2u * ((uint32_t)base * m1 + col0 + row);
+        c.fast = c.i0 + 2u * (uint32_t)((R - 1) * S) * m1 + 1u < n_steps;
+        return c;
+    }
+    __device__ __forceinline__ float2 get(const Ctx &c, int off) const
+    {
+        const float2 v = c.p[off * kTmaRows]; // rows that were not fetched hold junk: never used, see below
+        if (c.fast) return v;
+        const uint32_t i = c.i0 + 2u * (uint32_t)off * m1;
+        if (i + 1 < n_steps) return v;
+        return make_float2(i < n_steps ? v.x : mean, mean); // mean padding, demod_binary_resamp_cpu.c:130-133
+    }
+};
+
+__global__ void __launch_bounds__(512, 2)
+fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
+                     const uint32_t *__restrict__ n_steps_arr, const float *__restrict__ mean_arr, uint32_t m1, uint32_t m,
+                     const float2 *__restrict__ tw, const float2 *__restrict__ tb)
+{
+    constexpr int L = kTmaL, ROWS = kTmaRows, NS = cfg_stages(L), RL = cfg_radix(L, NS - 1);
+    static_assert(NS == 3 && RL == 8 && cfg_threads(L) == 512, "written for 2048 = 16 x 16 x 8 with 512 threads");
+    extern __shared__ __align__(128) float2 sm[];
+    __shared__ __align__(8) unsigned long long bar;
+    const int b = blockIdx.y;
+    const uint32_t col0 = blockIdx.x * ROWS;
+    const uint32_t n_steps = n_steps_arr[b];
+    const float mean = mean_arr[b];
+    // rows (positions m2) that hold at least one sample below n_steps; a row is 2*m1 samples
+    const uint32_t rows_needed = min((uint32_t)L, (n_steps + 2u * m1 - 1u) / (2u * m1));
+    const uint32_t boxes = (rows_needed + kTmaBox - 1) / kTmaBox;
+    const uint32_t bar_a = smem_addr(&bar);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(boxes * kTmaBox * ROWS * 8u) : "memory");
+        for (uint32_t k = 0; k < boxes; ++k)
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                             smem_addr(sm + k * kTmaBox * ROWS)),
+                         "l"(&in_map), "r"((int)(2u * col0)), "r"((int)(k * kTmaBox)), "r"(b), "r"(bar_a)
+                         : "memory");
+    }
+    __syncthreads();
+    {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n selp.u32 %0, 1, 0, p;\n}"
+                         : "=r"(done)
+                         : "r"(bar_a)
+                         : "memory");
+    }
+
+    SmemIO<L, ROWS, 3> io{sm};
+    const TmaDenseLoad dload{sm, m1, col0, n_steps, mean};
+    tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true>(tw, dload, io);
+    __syncthreads();
+    tile_middle<L, ROWS, 3, 1, NS - 1>(tw, sm);
+
+    // last stage: radix 8 over consecutive positions.  Lanes take butterflies in transposed order (bf = 16 (x % 16) + x / 16)
+    // so that a half-warp produces consecutive k2 and its dense stores cover 128 contiguous bytes.
+    constexpr int PER = ROWS * (L / RL) / 512; // butterflies per thread (2)
+    float2 v[PER][RL];
+    int rows_[PER], kb_[PER];
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+        const int item = threadIdx.x + it * 512;
+        const int row = item % ROWS, x = item / ROWS;
+        const int bf = 16 * (x % 16) + x / 16;
+        const int base = bf * RL;
+        rows_[it] = row;
+        kb_[it] = freq_of_pos<L>(base);
+        const float2 *c = io.begin(row, base);
+#pragma unroll
+        for (int j = 0; j < RL; ++j) v[it][j] = io.get(const_cast<float2 *>(c), j);
+    }
+    __syncthreads(); // the dense image overwrites the padded tile
+    const float inv_m = 1.0f / (float)m;
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+        Dft<RL>::run(v[it]);
+        const uint32_t col = col0 + rows_[it];
+        float sn, cs;
+        sincospif(-2.0f * (float)(col * (uint32_t)kb_[it]) * inv_m, &sn, &cs);
+        const float2 a = make_float2(cs, sn);
+        const float2 *__restrict__ t = tb + (size_t)col * RL;
+        float2 *d = sm + kb_[it] * ROWS + rows_[it];
+#pragma unroll
+        for (int q = 0; q < RL; ++q) {
+            const float2 w = (q == 0) ? a : cmul(a, __ldg(t + q));
+            d[q * (L / RL) * ROWS] = cmul(v[it][out_slot<RL>(q)], w);
+        }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < L / kTmaBox; ++k)
+            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&out_map),
+                         "r"((int)(2u * col0)), "r"(k * kTmaBox), "r"(b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
+                         : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
 }
 
@@ -439,7 +580,7 @@ struct Pass2Load {
 enum { PASS2_POWER = 0, PASS2_SPECTRUM = 1, PASS2_CONJ = 2 };
 
 template <int L, int ROWS, int MODE>
-__global__ void __launch_bounds__(cfg_threads(L), cfg_threads(L) == 512 ? 1 : 2)
+__global__ void __launch_bounds__(cfg_threads(L), cfg_ctas(L))
 fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
                  uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
                  const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
@@ -665,13 +806,70 @@ void brp_fft_plan_destroy(BrpFftPlan *p)
     memset(p, 0, sizeof(*p));
 }
 
+// ---- host side of the TMA pass 1: tensor maps over the input series and the intermediate array
+typedef CUresult (*tensor_map_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                         const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                         CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static tensor_map_encode_fn tensor_map_encoder()
+{
+    static tensor_map_encode_fn fn = nullptr;
+    static bool looked = false;
+    if (!looked) {
+        looked = true;
+        const char *off = getenv("BRP_FFT_TMA"); // BRP_FFT_TMA=0 selects the plain kernel (A/B measurements)
+        if (!(off && off[0] == '0')) {
+            void *sym = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+                fn = (tensor_map_encode_fn)sym;
+        }
+    }
+    return fn;
+}
+
+// [batch][m2 rows][2*m1 floats] with the given batch stride (in floats); box = 256 rows x 8 floats
+static bool encode_tile_map(tensor_map_encode_fn enc, CUtensorMap *map, const void *base, uint32_t m1, uint32_t m2, size_t batch_stride,
+                            int batch)
+{
+    if (((uintptr_t)base & 15) || (batch > 1 && (batch_stride & 3))) return false;
+    const cuuint64_t dims[3] = {2ull * m1, m2, (cuuint64_t)batch};
+    const cuuint64_t strides[2] = {8ull * m1, batch > 1 ? 4ull * batch_stride : 8ull * m1 * m2};
+    const cuuint32_t box[3] = {2 * kTmaRows, kTmaBox, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static bool pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride, const float2 *work, int batch, CUtensorMap *in_map,
+                           CUtensorMap *out_map)
+{
+    if (p.m2 != (uint32_t)kTmaL || p.m1 % kTmaRows != 0) return false;
+    tensor_map_encode_fn enc = tensor_map_encoder();
+    if (!enc) return false;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Layout<kTmaL, kTmaRows, 3>::BYTES) != cudaSuccess)
+            return false;
+        configured = true;
+    }
+    return encode_tile_map(enc, in_map, in, p.m1, p.m2, in_stride, batch) &&
+           encode_tile_map(enc, out_map, work, p.m1, p.m2, 2 * (size_t)p.m, batch);
+}
+
 static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, size_t in_stride, const uint32_t *n_steps,
                               const float *mean, float2 *work, float *out, size_t out_stride, uint32_t out_count, float norm,
                               int batch, cudaStream_t st, cudaEvent_t mid_event)
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
-    t1->p1<<<g1, t1->threads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
+    CUtensorMap in_map, out_map;
+    if (pass1_tma_maps(p, in, in_stride, work, batch, &in_map, &out_map))
+        fft_pass1_tma_kernel<<<g1, 512, Layout<kTmaL, kTmaRows, 3>::BYTES, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1,
+                                                                               p.tw_inter_hi);
+    else
+        t1->p1<<<g1, t1->threads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (mid_event) cudaEventRecord(mid_event, st);

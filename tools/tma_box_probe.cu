@@ -4,7 +4,7 @@
 //
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/tma_box_probe tools/tma_box_probe.cu && /tmp/tma_box_probe
 //
-// For W in {4, 8, 16} columns: persistent CTAs copy every tile of a 16-template volume A -> smem -> B.
+// For W in {2, 4, 8} columns: persistent CTAs copy every tile of a 16-template volume A -> smem -> B.
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -139,6 +139,8 @@ int main()
     run<4, false>(enc, a, b, sink, 3);
     run<4, true>(enc, a, b, sink, 2);
     run<4, true>(enc, a, b, sink, 3);
+    run<2, false>(enc, a, b, sink, 4);
+    run<2, true>(enc, a, b, sink, 4);
     run<8, false>(enc, a, b, sink, 1);
     run<8, true>(enc, a, b, sink, 1);
     return 0;
