@@ -620,6 +620,38 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
     // (k1' = (M1-k1) mod M1 on the self-mirrored row k2 = 0).
     //   E = (Z[k] + conj Z[M-k])/2,  O = (Z[k] - conj Z[M-k])/(2i)
     //   X[k] = E + W_N^k O,  X[M-k] = conj(E - W_N^k O)            (N = 2M)
+    if constexpr (L == 1024 && ROWS == 8 && MODE == PASS2_POWER) {
+        // Production shape, interior tiles (no self-mirrored row): thread t owns row r = t % 4 and k1 = t/4 + 64 it.  With
+        // 1024 = 32 x 32 the digit-reversed position of k1 = q0 + 32 q1 is 32 q0 + q1, so both shared-memory operands and
+        // both output addresses advance by constants per iteration and the whole index computation leaves the loop.
+        if (a >= 1 && 2 * (a + T2 - 1) < m2) {
+            using Lay = Layout<L, ROWS, 2>;
+            static_assert(Lay::C4 == 0 && Lay::C5 == 1 && Lay::C8 == 0 && cfg_threads(L) == 256, "address algebra below");
+            const int r = threadIdx.x & 3, k10 = threadIdx.x >> 2, q0 = k10 & 31, q10 = k10 >> 5;
+            const uint32_t k2 = a + r;
+            const float2 *pa = sm + r * Lay::PITCH + q0 * 33 + q10;
+            const float2 *pb = sm + (r + T2) * Lay::PITCH + (31 - q0) * 33 + (31 - q10);
+            const float2 wa = __ldg(&tw_a[k2]);
+            const float2 *__restrict__ twb = tw_b + k10;
+            const uint32_t k0 = k2 + m2 * (uint32_t)k10;
+            float *Pk = P + k0, *Pm = P + (m - k0);
+            const uint32_t step = 64u * m2;
+#pragma unroll
+            for (int it = 0; it < 16; ++it) {
+                const float2 za = pa[2 * it], zb = pb[-2 * it];
+                const float2 e = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
+                const float2 d = make_float2(0.5f * (za.x - zb.x), 0.5f * (za.y + zb.y));
+                const float2 o = make_float2(d.y, -d.x);
+                const float2 w = cmul(wa, __ldg(twb + 64 * it));
+                const float2 wo = cmul(w, o);
+                const float2 xp = cadd(e, wo), xm = csub(e, wo);
+                const uint32_t k = k0 + (uint32_t)it * step;
+                if (k < ps_count) Pk[(size_t)it * step] = norm * fmaf(xp.x, xp.x, xp.y * xp.y);
+                if (m - k < ps_count) Pm[-(ptrdiff_t)((size_t)it * step)] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+            }
+            return;
+        }
+    }
 #pragma unroll 4
     for (int item = threadIdx.x; item < T2 * (int)M1; item += cfg_threads(L)) {
         const int r = item % T2;
