@@ -83,7 +83,6 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
 {
     constexpr bool FAST = MODE != 0;
     __shared__ float2 s_tab[65];
-    __shared__ float2 s_ends[MODE == 2 ? 2 : 1][MODE == 2 ? kGroups + 1 : 1]; // (del_t, table cell) at the first sample of every group
     __shared__ int s_nsteps;
     __shared__ double s_warp[BRP_RESAMP_THREADS / 32];
     __shared__ bool s_last;
@@ -194,19 +193,21 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
             continue;
         }
         if constexpr (MODE == 2) {
-            // one evaluation per group of kGroupLen samples (lane l: group l of the warp's segment)
-            float2(&ends)[kGroups + 1] = s_ends[chunk & 1]; // double-buffered: one barrier per chunk
+            // one evaluation per group of kGroupLen samples (lane l: group l of the warp's segment); the right end of a
+            // group is its neighbour's left end, fetched by shuffle.  The right end of the warp's last group is evaluated
+            // by the warp itself (one more pass with one active lane) rather than fetched from the next warp through
+            // shared memory: no block barrier, warps run independently.
             const uint32_t g_lo = seg_lo + (uint32_t)lane * kGroupLen;
             int cell;
             const float d_own = brp_del_t_cell((float)g_lo, tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, cell);
-            ends[threadIdx.x] = make_float2(d_own, __int_as_float(cell));
-            if (threadIdx.x == BRP_RESAMP_THREADS - 1) { // right end of the chunk's last group
+            float2 eb;
+            eb.x = __shfl_down_sync(0xffffffffu, d_own, 1);
+            eb.y = __int_as_float(__shfl_down_sync(0xffffffffu, cell, 1));
+            if (lane == 31) {
                 int c2;
-                const float d2 = brp_del_t_cell((float)(g_lo + kGroupLen), tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, c2);
-                ends[kGroups] = make_float2(d2, __int_as_float(c2));
+                eb.x = brp_del_t_cell((float)(g_lo + kGroupLen), tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, c2);
+                eb.y = __int_as_float(c2);
             }
-            __syncthreads();
-            const float2 eb = ends[threadIdx.x + 1];
             const float base = (float)g_lo;
             const float lo = __fsub_rn(fminf(d_own, eb.x), eta), hi = __fadd_rn(fmaxf(d_own, eb.x), eta);
             const float a = __fsub_rn(base, hi);                                        // smallest i - x of the group
