@@ -406,7 +406,7 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
                  const float *__restrict__ mean_arr, float2 *__restrict__ work, uint32_t m1, uint32_t m,
                  const float2 *__restrict__ tw, const float2 *__restrict__ tb)
 {
-    extern __shared__ float2 sm[];
+    extern __shared__ __align__(128) float2 sm[];
     constexpr int NS = cfg_stages(L);
     const int b = blockIdx.y;
     const uint32_t col0 = blockIdx.x * ROWS;
@@ -579,13 +579,12 @@ struct Pass2Load {
 //         (backward real transform = conj(FFT(conj(.))), whitening pre-step; `ps_count` = number of float2 pairs wanted)
 enum { PASS2_POWER = 0, PASS2_SPECTRUM = 1, PASS2_CONJ = 2 };
 
-template <int L, int ROWS, int MODE>
-__global__ void __launch_bounds__(cfg_threads(L), cfg_ctas(L))
-fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
-                 uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
-                 const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
+template <int L, int ROWS, int MODE, bool TMA_OUT>
+__device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
+                                           uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
+                                           const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b, float2 *sm,
+                                           const CUtensorMap *out_map)
 {
-    extern __shared__ float2 sm[];
     constexpr int NS = cfg_stages(L);
     constexpr int T2 = ROWS / 2;
     constexpr uint32_t M1 = L;
@@ -636,6 +635,45 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
             const uint32_t k0 = k2 + m2 * (uint32_t)k10;
             float *Pk = P + k0, *Pm = P + (m - k0);
             const uint32_t step = 64u * m2;
+            if constexpr (TMA_OUT) {
+                // The 16-byte runs of this tile's outputs (four consecutive k2 per k1) cost one L1 tag lookup each when stored by
+                // the lanes.  The powers of the rows k2 = a..a+3 are therefore staged densely in shared memory, [k1][4] (over the
+                // tile, after everybody has read its operands), and four tensor stores (256 rows x 16 bytes) write them out; rows
+                // at or beyond ps_count / m2 are clipped by the tensor map.  The mirror rows m2-a-3..m2-a start one float past a
+                // 16-byte boundary, which a tensor copy cannot address, so they keep the per-lane stores.
+                float2 za[16], zb[16];
+#pragma unroll
+                for (int it = 0; it < 16; ++it) {
+                    za[it] = pa[2 * it];
+                    zb[it] = pb[-2 * it];
+                }
+                __syncthreads();
+                float *stage_a = reinterpret_cast<float *>(sm); // 1024 x 4 floats
+#pragma unroll
+                for (int it = 0; it < 16; ++it) {
+                    const float2 e = make_float2(0.5f * (za[it].x + zb[it].x), 0.5f * (za[it].y - zb[it].y));
+                    const float2 d = make_float2(0.5f * (za[it].x - zb[it].x), 0.5f * (za[it].y + zb[it].y));
+                    const float2 o = make_float2(d.y, -d.x);
+                    const float2 w = cmul(wa, __ldg(twb + 64 * it));
+                    const float2 wo = cmul(w, o);
+                    const float2 xp = cadd(e, wo), xm = csub(e, wo);
+                    stage_a[4 * (k10 + 64 * it) + r] = norm * fmaf(xp.x, xp.x, xp.y * xp.y);
+                    const uint32_t k = k0 + (uint32_t)it * step;
+                    if (m - k < ps_count) Pm[-(ptrdiff_t)((size_t)it * step)] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncthreads();
+                if (threadIdx.x == 0) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(out_map),
+                                     "r"((int)a), "r"(256 * j), "r"(b), "r"(smem_addr(stage_a + 1024 * j))
+                                     : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                }
+                return;
+            }
 #pragma unroll
             for (int it = 0; it < 16; ++it) {
                 const float2 za = pa[2 * it], zb = pb[-2 * it];
@@ -685,6 +723,26 @@ fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t
             if (km < ps_count && km != k) P[km] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
         }
     }
+}
+
+template <int L, int ROWS, int MODE>
+__global__ void __launch_bounds__(cfg_threads(L), cfg_ctas(L))
+fft_pass2_kernel(const float2 *__restrict__ work, float *__restrict__ ps, size_t ps_stride, uint32_t ps_count,
+                 uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
+                 const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
+{
+    extern __shared__ __align__(128) float2 sm[];
+    pass2_body<L, ROWS, MODE, false>(work, ps, ps_stride, ps_count, m2, m, norm, tw, tw_a, tw_b, sm, nullptr);
+}
+
+// production shape of the per-template hot path: powers leave through tensor stores (see pass2_body)
+__global__ void __launch_bounds__(256, 2)
+fft_pass2_tma_kernel(const __grid_constant__ CUtensorMap out_map, const float2 *__restrict__ work, float *__restrict__ ps,
+                     size_t ps_stride, uint32_t ps_count, uint32_t m2, uint32_t m, float norm, const float2 *__restrict__ tw,
+                     const float2 *__restrict__ tw_a, const float2 *__restrict__ tw_b)
+{
+    extern __shared__ __align__(128) float2 sm[];
+    pass2_body<1024, 8, PASS2_POWER, true>(work, ps, ps_stride, ps_count, m2, m, norm, tw, tw_a, tw_b, sm, &out_map);
 }
 
 // ------------------------------------------------------------------ host side
@@ -890,6 +948,31 @@ static bool pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_strid
            encode_tile_map(enc, out_map, work, p.m1, p.m2, 2 * (size_t)p.m, batch);
 }
 
+// Power spectrum as [batch][rows k1][m2 floats]; only the rows that hold a bin below `count` exist in the map, so the
+// tensor stores of pass 2 clip everything else.  The last of those rows is written whole: the caller's buffer must hold
+// m2 * ceil(count / m2) floats per template (out_stride says how many it holds).
+static bool pass2_tma_map(const BrpFftPlan &p, const float *out, size_t out_stride, uint32_t count, int batch, CUtensorMap *map)
+{
+    if (p.m1 != 1024 || p.m2 < 16 || count == 0 || count > p.m) return false;
+    const uint32_t rows = (count + p.m2 - 1) / p.m2;
+    if ((size_t)rows * p.m2 > out_stride || (out_stride & 3) || ((uintptr_t)out & 15)) return false;
+    tensor_map_encode_fn enc = tensor_map_encoder();
+    if (!enc) return false;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute((const void *)fft_pass2_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Layout<1024, 8, 2>::BYTES) != cudaSuccess)
+            return false;
+        configured = true;
+    }
+    const cuuint64_t dims[3] = {p.m2, rows, (cuuint64_t)batch};
+    const cuuint64_t strides[2] = {4ull * p.m2, 4ull * out_stride};
+    const cuuint32_t box[3] = {4, 256, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(out), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, size_t in_stride, const uint32_t *n_steps,
                               const float *mean, float2 *work, float *out, size_t out_stride, uint32_t out_count, float norm,
                               int batch, cudaStream_t st, cudaEvent_t mid_event)
@@ -907,6 +990,12 @@ static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, si
     if (mid_event) cudaEventRecord(mid_event, st);
     const int T2 = t2->rows / 2;
     const dim3 g2((p.m2 / 2 + 1 + T2 - 1) / T2, batch); // rows k2 = 0 .. m2/2
+    CUtensorMap ps_map;
+    if (mode == PASS2_POWER && pass2_tma_map(p, out, out_stride, out_count, batch, &ps_map)) {
+        fft_pass2_tma_kernel<<<g2, 256, Layout<1024, 8, 2>::BYTES, st>>>(ps_map, work, out, out_stride, out_count, p.m2, p.m, norm,
+                                                                       p.tw_pass2, p.tw_untangle_a, p.tw_untangle_b);
+        return cudaGetLastError();
+    }
     const pass2_fn k2 = mode == PASS2_POWER ? t2->p2 : (mode == PASS2_SPECTRUM ? t2->p2_spectrum : t2->p2_conj);
     k2<<<g2, t2->threads, t2->smem2, st>>>(work, out, out_stride, out_count, p.m2, p.m, norm, p.tw_pass2, p.tw_untangle_a,
                                          p.tw_untangle_b);

@@ -74,8 +74,11 @@ __device__ __forceinline__ double warp_sum(double v)
 
 // MODE 0: index by the literal double arithmetic (series longer than 2^22); 1: FP32 index path, every sample
 // evaluated; 2: FP32 index path with run detection.
+#ifndef BRP_RESAMP_MIN_BLOCKS
+#define BRP_RESAMP_MIN_BLOCKS 8
+#endif
 template <int MODE, bool WRITE_IDX>
-__global__ void __launch_bounds__(BRP_RESAMP_THREADS, 8)
+__global__ void __launch_bounds__(BRP_RESAMP_THREADS, BRP_RESAMP_MIN_BLOCKS)
 resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restrict__ tmpl, BrpGeomDev g,
                 float *__restrict__ out, size_t out_stride, int32_t *__restrict__ idx_out,
                 uint32_t *__restrict__ n_steps_out, float *__restrict__ mean_out, double *__restrict__ partials,

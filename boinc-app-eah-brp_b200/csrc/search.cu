@@ -147,7 +147,9 @@ int brp_search_create(brp_search **out, int device, const brp_geometry *g, float
     rc = brp_fft_plan_create(&s->plan, g->nsamples);
     if (rc) { free(s); return rc; }
     s->rs_stride = ((size_t)g->nsamples_unpadded + 3) & ~(size_t)3;
-    s->ps_stride = (((size_t)g->harmonic_idx_hi + 4) + 31) & ~(size_t)31; // bulk copies round slices up to 16 bytes
+    // the harmonic-summing bulk copies round slices up to 16 bytes; the tensor stores of FFT pass 2 write the last row of
+    // the stored part of the spectrum whole (a row is at most 6144 bins)
+    s->ps_stride = (((size_t)g->harmonic_idx_hi + 6144 + 4) + 31) & ~(size_t)31;
     s->nblk = brp_resamp_blocks(g->nsamples_unpadded);
     s->hit_cap = 5u * (g->fundamental_idx_hi ? g->fundamental_idx_hi : 1u);
     const size_t B = max_batch;
