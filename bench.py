@@ -281,6 +281,8 @@ def run_ours(args):
         roofline = {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["GBps"], "peak": peak, "peak_source": peak_src,
                     "unit": "GB/s", "frac": stages[dom]["GBps"] / peak, "traffic": traffic,
                     "algorithmic_bytes_per_template": alg, "templates_per_launch": nb, "stages": stages,
+                    "note": "stage fractions are algorithmic bytes / CUDA-event time / HBM peak; the resampler's 4*Nu input bytes per template "
+                            "come from L2 (the series is shared by the batch), so its fraction can exceed 1",
                     "whole_loop": {"GBps": alg["total"] * value / 1e9, "frac": alg["total"] * value / 1e9 / peak}}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
