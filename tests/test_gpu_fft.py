@@ -105,3 +105,40 @@ def test_full_size_properties(n):
         want_k = abs(np.dot(xd, ph)) ** 2 / n
         assert abs(got[k] - want_k) <= 1e-4 * max(want_k, 1.0)
     s.close()
+
+
+_TMA_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1])
+import brp_b200
+from brp_b200 import synth
+nu = 1 << 22
+series, _ = synth.make_series(nu, seed=77)
+g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, 1.0, 400.0, 1000)
+s = brp_b200.Search(g, max_batch=1)
+s.set_series(series)
+t = brp_b200.derive_template(1462.994097917309, 0.192481315985, 1.753485476554, g.step_inv)
+s.stage_resample(t, want_series=False, want_index=False)
+np.save(sys.argv[2], s.stage_spectrum(g.harmonic_idx_hi))
+s.close()
+"""
+
+
+def test_tensor_copy_kernels_equal_the_plain_kernels_bit_for_bit(tmp_path):
+    """The production FFT kernels (tiles moved by TMA tensor copies, fft_pass1_tma_kernel / fft_pass2_tma_kernel) do the same
+    arithmetic as the plain kernels every other shape uses; BRP_FFT_TMA=0 selects the plain ones.  Same work-unit, same
+    template, two processes: the power spectra must be identical bit patterns."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parent.parent)
+    outs = []
+    for flag in ("1", "0"):
+        out = tmp_path / f"ps_{flag}.npy"
+        env = dict(os.environ, BRP_FFT_TMA=flag)
+        r = subprocess.run([sys.executable, "-c", _TMA_SCRIPT, root, str(out)], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(np.load(out))
+    assert outs[0].size > 1_000_000 and np.all(np.isfinite(outs[0])) and outs[0][1:].min() >= 0 and outs[0].max() > 0
+    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
