@@ -619,23 +619,29 @@ __device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, floa
     // (k1' = (M1-k1) mod M1 on the self-mirrored row k2 = 0).
     //   E = (Z[k] + conj Z[M-k])/2,  O = (Z[k] - conj Z[M-k])/(2i)
     //   X[k] = E + W_N^k O,  X[M-k] = conj(E - W_N^k O)            (N = 2M)
-    if constexpr (L == 1024 && ROWS == 8 && MODE == PASS2_POWER) {
-        // Production shape, interior tiles (no self-mirrored row): thread t owns row r = t % 4 and k1 = t/4 + 64 it.  With
-        // 1024 = 32 x 32 the digit-reversed position of k1 = q0 + 32 q1 is 32 q0 + q1, so both shared-memory operands and
-        // both output addresses advance by constants per iteration and the whole index computation leaves the loop.
+    // Interior tiles (no self-mirrored row): thread t owns row r = t % T2 and k1 = t / T2 + KSTEP it.  KSTEP is a multiple of
+    // L / R_last, so only the last digit of k1 changes from one iteration to the next: the digit-reversed position (and its
+    // padded address, the padding units being multiples of R_last) advances by the constant CPOS, the mirror operand recedes
+    // by it, and the whole index computation leaves the loop.
+    constexpr int NT2 = cfg_threads(L), RL2 = cfg_radix(L, NS - 1), KSTEP = NT2 / T2, UNIT = L / RL2;
+    constexpr bool AFFINE = MODE == PASS2_POWER && NT2 % T2 == 0 && KSTEP % UNIT == 0 && (T2 * L) % NT2 == 0;
+    if constexpr (AFFINE) {
         if (a >= 1 && 2 * (a + T2 - 1) < m2) {
             using Lay = Layout<L, ROWS, 2>;
-            static_assert(Lay::C4 == 0 && Lay::C5 == 1 && Lay::C8 == 0 && cfg_threads(L) == 256, "address algebra below");
-            const int r = threadIdx.x & 3, k10 = threadIdx.x >> 2, q0 = k10 & 31, q10 = k10 >> 5;
+            constexpr int CPOS = KSTEP / UNIT, ITERS = T2 * L / NT2;
+            static_assert((Lay::C4 == 0 || 16 % RL2 == 0) && (Lay::C5 == 0 || 32 % RL2 == 0) && (Lay::C8 == 0 || 256 % RL2 == 0),
+                          "padding units must be multiples of the last radix");
+            const int r = threadIdx.x % T2, k10 = threadIdx.x / T2;
             const uint32_t k2 = a + r;
-            const float2 *pa = sm + r * Lay::PITCH + q0 * 33 + q10;
-            const float2 *pb = sm + (r + T2) * Lay::PITCH + (31 - q0) * 33 + (31 - q10);
+            const float2 *pa = io.begin(r, pos_of_freq<L>(k10));
+            const float2 *pb = io.begin(r + T2, pos_of_freq<L>((int)L - 1 - k10));
             const float2 wa = __ldg(&tw_a[k2]);
             const float2 *__restrict__ twb = tw_b + k10;
             const uint32_t k0 = k2 + m2 * (uint32_t)k10;
             float *Pk = P + k0, *Pm = P + (m - k0);
-            const uint32_t step = 64u * m2;
+            const uint32_t step = (uint32_t)KSTEP * m2;
             if constexpr (TMA_OUT) {
+                static_assert(L == 1024 && ROWS == 8 && ITERS == 16 && CPOS == 2 && KSTEP == 64, "staging image below is written for this shape");
                 // The 16-byte runs of this tile's outputs (four consecutive k2 per k1) cost one L1 tag lookup each when stored by
                 // the lanes.  The powers of the rows k2 = a..a+3 are therefore staged densely in shared memory, [k1][4] (over the
                 // tile, after everybody has read its operands), and four tensor stores (256 rows x 16 bytes) write them out; rows
@@ -675,12 +681,12 @@ __device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, floa
                 return;
             }
 #pragma unroll
-            for (int it = 0; it < 16; ++it) {
-                const float2 za = pa[2 * it], zb = pb[-2 * it];
+            for (int it = 0; it < ITERS; ++it) {
+                const float2 za = pa[CPOS * it], zb = pb[-CPOS * it];
                 const float2 e = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
                 const float2 d = make_float2(0.5f * (za.x - zb.x), 0.5f * (za.y + zb.y));
                 const float2 o = make_float2(d.y, -d.x);
-                const float2 w = cmul(wa, __ldg(twb + 64 * it));
+                const float2 w = cmul(wa, __ldg(twb + KSTEP * it));
                 const float2 wo = cmul(w, o);
                 const float2 xp = cadd(e, wo), xm = csub(e, wo);
                 const uint32_t k = k0 + (uint32_t)it * step;
