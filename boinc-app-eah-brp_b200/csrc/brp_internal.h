@@ -62,7 +62,8 @@ void brp_fft_plan_destroy(BrpFftPlan *p);
 // work: batch x m float2; ps: batch x ps_stride floats, bins [0, ps_count) written, ps[0] = 0.
 cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in_stride, const uint32_t *n_steps,
                                  const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
-                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event);
+                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event,
+                                 uint32_t n_steps_bound = 0 /* upper bound of every n_steps[b] if the caller knows one (e.g. Nu) */);
 
 cudaError_t brp_launch_fft_spectrum(const BrpFftPlan &p, const float *in, const uint32_t *n_steps, const float *mean,
                                     float2 *work, float2 *spectrum, uint32_t count, cudaStream_t st);

@@ -437,12 +437,18 @@ constexpr int kTmaL = 2048, kTmaRows = 4, kTmaBox = 256;
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// THIRD < 0: plain length-2048 pass.  THIRD = q in 0..2: the tile is sub-transform q of a length-6144 pass whose upper two
+// thirds are mean padding (see fft_pass1_tma_kernel): the value handed to the 2048-point stages is the radix-3 output
+// y_q[p] = (x_p + c (W3^q + W3^2q)) W_6144^{q p}, c = (mean, mean), i.e. x + 2c for q = 0 and (x - c) W^{qp} otherwise.
 struct TmaDenseLoad {
     const float2 *dense;
     uint32_t m1, col0, n_steps;
     float mean;
+    int third;
+    const float2 *tw3; // W_6144^{q p}, p < 2048 (third > 0)
     struct Ctx {
         const float2 *p;
+        const float2 *t;
         uint32_t i0;
         bool fast;
     };
@@ -451,25 +457,39 @@ struct TmaDenseLoad {
         constexpr int R = cfg_radix(kTmaL, 0), S = cfg_stride(kTmaL, 0);
         Ctx c;
         c.p = dense + base * kTmaRows + row;
+        c.t = tw3 + base;
         c.i0 = 2u * ((uint32_t)base * m1 + col0 + row);
         c.fast = c.i0 + 2u * (uint32_t)((R - 1) * S) * m1 + 1u < n_steps;
         return c;
     }
     __device__ __forceinline__ float2 get(const Ctx &c, int off) const
     {
-        const float2 v = c.p[off * kTmaRows]; // rows that were not fetched hold junk: never used, see below
-        if (c.fast) return v;
-        const uint32_t i = c.i0 + 2u * (uint32_t)off * m1;
-        if (i + 1 < n_steps) return v;
-        return make_float2(i < n_steps ? v.x : mean, mean); // mean padding, demod_binary_resamp_cpu.c:130-133
+        float2 v = c.p[off * kTmaRows]; // rows that were not fetched hold junk: never used, see below
+        if (!c.fast) {
+            const uint32_t i = c.i0 + 2u * (uint32_t)off * m1;
+            if (i + 1 >= n_steps) v = make_float2(i < n_steps ? v.x : mean, mean); // mean padding, demod_binary_resamp_cpu.c:130-133
+        }
+        if (third < 0) return v;
+        if (third == 0) return cadd(v, make_float2(mean + mean, mean + mean));
+        return cmul(make_float2(fmaf(-0.5f, mean + mean, v.x), fmaf(-0.5f, mean + mean, v.y)), __ldg(c.t + off));
     }
 };
 
+// THIRDS = 3: pass-1 length 6144 = 3 x 2048 when only the first third of the rows can hold samples (n_steps <= Nu <= N/3, the
+// reference's production padding -P 3.0).  The radix-3 first stage then has two constant inputs, its three output blocks are
+// independent 2048-point transforms of values derived from the same 2048 loaded rows, and output k2 = 3 k' + q of block q
+// lands in row 3 k' + q.  One CTA per (column tile, q): same tile engine as the 2048 case, the radix-3 stage folded into
+// the load (same butterfly values as the generic radix-3 stage on these inputs; W^{2p} is read from the table instead of
+// being squared from W^p), a 4-D tensor map for the strided rows.
+template <int THIRDS>
 __global__ void __launch_bounds__(512, 2)
 fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
                      const uint32_t *__restrict__ n_steps_arr, const float *__restrict__ mean_arr, uint32_t m1, uint32_t m,
-                     const float2 *__restrict__ tw, const float2 *__restrict__ tb)
+                     const float2 *__restrict__ tw_all, const float2 *__restrict__ tb)
 {
+    const int third = THIRDS == 3 ? (int)blockIdx.z : -1;
+    // in-tile twiddles of the 2048-point stages: the table of the 6144 plan starts with the 2 x 2048 radix-3 entries
+    const float2 *__restrict__ tw = THIRDS == 3 ? tw_all + 2 * kTmaL : tw_all;
     constexpr int L = kTmaL, ROWS = kTmaRows, NS = cfg_stages(L), RL = cfg_radix(L, NS - 1);
     static_assert(NS == 3 && RL == 8 && cfg_threads(L) == 512, "written for 2048 = 16 x 16 x 8 with 512 threads");
     extern __shared__ __align__(128) float2 sm[];
@@ -503,7 +523,7 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     }
 
     SmemIO<L, ROWS, 3> io{sm};
-    const TmaDenseLoad dload{sm, m1, col0, n_steps, mean};
+    const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, third, third > 0 ? tw_all + (third - 1) * kTmaL : tw_all};
     tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true>(tw, dload, io);
     __syncthreads();
     tile_middle<L, ROWS, 3, 1, NS - 1>(tw, sm);
@@ -532,7 +552,8 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
         Dft<RL>::run(v[it]);
         const uint32_t col = col0 + rows_[it];
         float sn, cs;
-        sincospif(-2.0f * (float)(col * (uint32_t)kb_[it]) * inv_m, &sn, &cs);
+        const uint32_t k2b = THIRDS == 3 ? 3u * (uint32_t)kb_[it] + (uint32_t)third : (uint32_t)kb_[it];
+        sincospif(-2.0f * (float)(col * k2b) * inv_m, &sn, &cs);
         const float2 a = make_float2(cs, sn);
         const float2 *__restrict__ t = tb + (size_t)col * RL;
         float2 *d = sm + kb_[it] * ROWS + rows_[it];
@@ -546,10 +567,16 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     __syncthreads();
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int k = 0; k < L / kTmaBox; ++k)
-            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&out_map),
-                         "r"((int)(2u * col0)), "r"(k * kTmaBox), "r"(b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
-                         : "memory");
+        for (int k = 0; k < L / kTmaBox; ++k) {
+            if constexpr (THIRDS == 3)
+                asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%1, %2, %3, %4}], [%5];" ::"l"(&out_map),
+                             "r"((int)(2u * col0)), "r"(third), "r"(k * kTmaBox), "r"(b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
+                             : "memory");
+            else
+                asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&out_map),
+                             "r"((int)(2u * col0)), "r"(k * kTmaBox), "r"(b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
+                             : "memory");
+        }
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
@@ -937,21 +964,40 @@ static bool encode_tile_map(tensor_map_encode_fn enc, CUtensorMap *map, const vo
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-static bool pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride, const float2 *work, int batch, CUtensorMap *in_map,
-                           CUtensorMap *out_map)
+// returns 0 (use the plain kernel), 1 (2048-row tiles) or 3 (three 2048-row sub-transforms of a 6144-row pass)
+static int pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride, const float2 *work, int batch, uint32_t n_steps_bound,
+                          CUtensorMap *in_map, CUtensorMap *out_map)
 {
-    if (p.m2 != (uint32_t)kTmaL || p.m1 % kTmaRows != 0) return false;
+    if (p.m1 % kTmaRows != 0) return 0;
+    int thirds = 0;
+    if (p.m2 == (uint32_t)kTmaL) thirds = 1;
+    // 3 x 2048: only valid when no sample can sit beyond row 2048 (a row is 2*m1 samples)
+    else if (p.m2 == 3u * kTmaL && n_steps_bound != 0 && n_steps_bound <= 2u * p.m1 * (uint32_t)kTmaL) thirds = 3;
+    else return 0;
     tensor_map_encode_fn enc = tensor_map_encoder();
-    if (!enc) return false;
+    if (!enc) return 0;
     static bool configured = false;
     if (!configured) {
-        if (cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Layout<kTmaL, kTmaRows, 3>::BYTES) != cudaSuccess ||
+            cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  Layout<kTmaL, kTmaRows, 3>::BYTES) != cudaSuccess)
-            return false;
+            return 0;
         configured = true;
     }
-    return encode_tile_map(enc, in_map, in, p.m1, p.m2, in_stride, batch) &&
-           encode_tile_map(enc, out_map, work, p.m1, p.m2, 2 * (size_t)p.m, batch);
+    if (!encode_tile_map(enc, in_map, in, p.m1, p.m2, in_stride, batch)) return 0;
+    if (thirds == 1) return encode_tile_map(enc, out_map, work, p.m1, p.m2, 2 * (size_t)p.m, batch) ? 1 : 0;
+    // rows 3 k' + q of the intermediate as [batch][k'][q][2*m1 floats]
+    if ((uintptr_t)work & 15) return 0;
+    const cuuint64_t dims[4] = {2ull * p.m1, 3, (cuuint64_t)kTmaL, (cuuint64_t)batch};
+    const cuuint64_t strides[3] = {8ull * p.m1, 24ull * p.m1, 8ull * p.m};
+    const cuuint32_t box[4] = {2 * kTmaRows, 1, kTmaBox, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    return enc(out_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float2 *>(work), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS
+               ? 3
+               : 0;
 }
 
 // Power spectrum as [batch][rows k1][m2 floats]; only the rows that hold a bin below `count` exist in the map, so the
@@ -981,14 +1027,18 @@ static bool pass2_tma_map(const BrpFftPlan &p, const float *out, size_t out_stri
 
 static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, size_t in_stride, const uint32_t *n_steps,
                               const float *mean, float2 *work, float *out, size_t out_stride, uint32_t out_count, float norm,
-                              int batch, cudaStream_t st, cudaEvent_t mid_event)
+                              int batch, cudaStream_t st, cudaEvent_t mid_event, uint32_t n_steps_bound = 0)
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
     CUtensorMap in_map, out_map;
-    if (pass1_tma_maps(p, in, in_stride, work, batch, &in_map, &out_map))
-        fft_pass1_tma_kernel<<<g1, 512, Layout<kTmaL, kTmaRows, 3>::BYTES, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1,
-                                                                               p.tw_inter_hi);
+    const int thirds = pass1_tma_maps(p, in, in_stride, work, batch, n_steps_bound, &in_map, &out_map);
+    if (thirds == 1)
+        fft_pass1_tma_kernel<1><<<g1, 512, Layout<kTmaL, kTmaRows, 3>::BYTES, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1,
+                                                                                  p.tw_inter_hi);
+    else if (thirds == 3)
+        fft_pass1_tma_kernel<3><<<dim3(p.m1 / kTmaRows, batch, 3), 512, Layout<kTmaL, kTmaRows, 3>::BYTES, st>>>(
+            in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     else
         t1->p1<<<g1, t1->threads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     cudaError_t e = cudaGetLastError();
@@ -1010,9 +1060,10 @@ static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, si
 
 cudaError_t brp_launch_fft_power(const BrpFftPlan &p, const float *in, size_t in_stride, const uint32_t *n_steps,
                                  const float *mean, float2 *work, float *ps, size_t ps_stride, uint32_t ps_count,
-                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event)
+                                 float norm, int batch, cudaStream_t st, cudaEvent_t mid_event, uint32_t n_steps_bound)
 {
-    return launch_fft(p, PASS2_POWER, in, in_stride, n_steps, mean, work, ps, ps_stride, ps_count, norm, batch, st, mid_event);
+    return launch_fft(p, PASS2_POWER, in, in_stride, n_steps, mean, work, ps, ps_stride, ps_count, norm, batch, st, mid_event,
+                      n_steps_bound);
 }
 
 // X[0..count) of the real-input transform of `in` (n reals; samples >= *n_steps read as *mean), count <= n/2 + 1

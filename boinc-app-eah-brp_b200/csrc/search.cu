@@ -285,7 +285,7 @@ static int run_batch(brp_search *s, const BrpLane &ln, uint32_t first, uint32_t 
            RADPUL_CUDA_KERNEL_INVOKE);
     if (ev) cudaEventRecord(ev[1], ln.st);
     CU_TRY(brp_launch_fft_power(s->plan, ln.resamp, s->rs_stride, ln.nsteps, ln.mean, ln.work, ln.ps, s->ps_stride,
-                                s->g.harmonic_idx_hi, norm, (int)nb, ln.st, ev ? ev[2] : NULL),
+                                s->g.harmonic_idx_hi, norm, (int)nb, ln.st, ev ? ev[2] : NULL, s->g.nsamples_unpadded),
            RADPUL_CUDA_FFT_EXEC);
     if (ev) cudaEventRecord(ev[3], ln.st);
     CU_TRY(brp_launch_harmonic_summing(ln.ps, s->ps_stride, (int)nb, s->gd, s->thr, first_global + first, keys, ln.st),
