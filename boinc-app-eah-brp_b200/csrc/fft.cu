@@ -17,12 +17,17 @@
 //       the pairs (Z[k], Z[M-k]) the real-input "untangle" needs, so the epilogue forms
 //       X[k] = E + W_N^k O, X[M-k] = conj(E - W_N^k O) and stores norm*|X|^2 for bins < count only.
 //
-// In a tile every thread keeps a radix-16 (or 8/4/2/3) butterfly in registers; stages exchange data
-// through shared memory (decimation in frequency, in place, digit-reversed result), the first stage
-// reads straight from global memory and pass 1's last stage writes straight back, so a tile crosses
-// shared memory once per stage boundary only.  Shared-memory positions are padded (+1 per 16 and per
-// 256 elements) so the power-of-two strides of the butterflies and the digit-reversed reads of the
-// epilogue stay free of bank conflicts.
+// In a tile every thread keeps a radix-16 (or 32/8/4/2/3) butterfly in registers; stages exchange data through shared
+// memory (decimation in frequency, in place, digit-reversed result).  Shared-memory positions are padded and lanes
+// permuted per tile shape (Layout<>, chosen with tools/bank_conflicts.py and tools/pass1_tma_layout.py) so the
+// power-of-two strides of the butterflies and the digit-reversed reads of the epilogue stay free of bank conflicts.
+//
+// Global traffic.  A pass-1 tile is a few columns wide (32-byte runs 8 KB apart) and pass 2 writes 16-byte runs: moved
+// by the lanes, every run costs an L1 tag lookup, and those lookups -- not HBM, not issue slots -- bounded both kernels.
+// For the production shapes the tiles therefore travel by TMA tensor copies (fft_pass1_tma_kernel, fft_pass2_tma_kernel:
+// dense tile images in shared memory, cp.async.bulk.tensor boxes of 256 rows); every other shape uses the plain kernels
+// (fft_pass1_kernel, fft_pass2_kernel), whose first stage reads straight from global memory and whose last stage writes
+// straight back.  Both families do the same arithmetic (tests/test_gpu_fft.py compares them bit for bit).
 //
 // HBM traffic per template: 4N (x) + 8M (Y out) + 8M (Y in) + 4*count (P) = 12N + 4*count bytes,
 // against the algorithmic 4N + 4F of SURVEY.md 8(d).
