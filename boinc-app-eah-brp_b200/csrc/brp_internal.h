@@ -52,11 +52,17 @@ struct BrpFftPlan {
     float2 *tw_untangle_a; // W_n^{k2},      k2 < m2
     float2 *tw_untangle_b; // W_{2 m1}^{k1}, k1 < m1
     float2 *tw_inter_hi, *tw_inter_lo; // W_m^{p}: p = hi*1024 + lo
+    // pass 1 as `parts` sub-transforms of 2048 rows (m2 = parts*2048, upper rows all padding): W_{m2}^{q p} for q = 1..parts-1,
+    // p < 2048, and the second inter-pass factor for a last radix of 8, exp(-2 pi i col q / (8 m1))
+    int parts;
+    float2 *tw_parts, *tw_inter_parts;
     int smem_pass1, smem_pass2;
     int launches_per_batch;
 };
 
-int brp_fft_plan_create(BrpFftPlan *p, uint32_t n);
+// nu_hint: number of samples that can be valid (Nu) if the caller knows it, else 0; it may move the split of m so that
+// pass 1 can run as sub-transforms of 2048 rows (see fft.cu)
+int brp_fft_plan_create(BrpFftPlan *p, uint32_t n, uint32_t nu_hint = 0);
 void brp_fft_plan_destroy(BrpFftPlan *p);
 // in: batch x in_stride floats (only [0, n_steps[b]) valid; the rest is taken as mean[b]);
 // work: batch x m float2; ps: batch x ps_stride floats, bins [0, ps_count) written, ps[0] = 0.

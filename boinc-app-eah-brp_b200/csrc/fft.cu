@@ -442,15 +442,16 @@ constexpr int kTmaL = 2048, kTmaRows = 4, kTmaBox = 256;
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-// THIRD < 0: plain length-2048 pass.  THIRD = q in 0..2: the tile is sub-transform q of a length-6144 pass whose upper two
-// thirds are mean padding (see fft_pass1_tma_kernel): the value handed to the 2048-point stages is the radix-3 output
-// y_q[p] = (x_p + c (W3^q + W3^2q)) W_6144^{q p}, c = (mean, mean), i.e. x + 2c for q = 0 and (x - c) W^{qp} otherwise.
+// PART < 0: plain length-2048 pass.  PART = q in 0..parts-1: the tile is sub-transform q of a length parts*2048 pass whose rows
+// beyond the first 2048 are all mean padding (see fft_pass1_tma_kernel): the value handed to the 2048-point stages is the
+// output q of the radix-`parts` first stage, y_q[p] = (x_p + c sum_{j>0} W_parts^{jq}) W_{m2}^{q p} with c = (mean, mean), i.e.
+// x + (parts-1) c for q = 0 and (x - c) W^{qp} otherwise.
 struct TmaDenseLoad {
     const float2 *dense;
     uint32_t m1, col0, n_steps;
     float mean;
-    int third;
-    const float2 *tw3; // W_6144^{q p}, p < 2048 (third > 0)
+    int part, parts;
+    const float2 *twq; // W_{m2}^{q p}, p < 2048 (part > 0)
     struct Ctx {
         const float2 *p;
         const float2 *t;
@@ -462,7 +463,7 @@ struct TmaDenseLoad {
         constexpr int R = cfg_radix(kTmaL, 0), S = cfg_stride(kTmaL, 0);
         Ctx c;
         c.p = dense + base * kTmaRows + row;
-        c.t = tw3 + base;
+        c.t = twq + base;
         c.i0 = 2u * ((uint32_t)base * m1 + col0 + row);
         c.fast = c.i0 + 2u * (uint32_t)((R - 1) * S) * m1 + 1u < n_steps;
         return c;
@@ -474,27 +475,27 @@ struct TmaDenseLoad {
             const uint32_t i = c.i0 + 2u * (uint32_t)off * m1;
             if (i + 1 >= n_steps) v = make_float2(i < n_steps ? v.x : mean, mean); // mean padding, demod_binary_resamp_cpu.c:130-133
         }
-        if (third < 0) return v;
-        if (third == 0) return cadd(v, make_float2(mean + mean, mean + mean));
-        return cmul(make_float2(fmaf(-0.5f, mean + mean, v.x), fmaf(-0.5f, mean + mean, v.y)), __ldg(c.t + off));
+        if (part < 0) return v;
+        const float c2 = mean + mean; // parts = 3: the same operations as Dft<3> on (v, c, c)
+        if (part == 0) return parts == 3 ? cadd(v, make_float2(c2, c2)) : cadd(v, make_float2(mean, mean));
+        const float2 d = parts == 3 ? make_float2(fmaf(-0.5f, c2, v.x), fmaf(-0.5f, c2, v.y)) : make_float2(v.x - mean, v.y - mean);
+        return cmul(d, __ldg(c.t + off));
     }
 };
 
-// THIRDS = 3: pass-1 length 6144 = 3 x 2048 when only the first third of the rows can hold samples (n_steps <= Nu <= N/3, the
-// reference's production padding -P 3.0).  The radix-3 first stage then has two constant inputs, its three output blocks are
-// independent 2048-point transforms of values derived from the same 2048 loaded rows, and output k2 = 3 k' + q of block q
-// lands in row 3 k' + q.  One CTA per (column tile, q): same tile engine as the 2048 case, the radix-3 stage folded into
-// the load (same butterfly values as the generic radix-3 stage on these inputs; W^{2p} is read from the table instead of
-// being squared from W^p), a 4-D tensor map for the strided rows.
-template <int THIRDS>
+// PARTS = 2, 3: pass-1 length PARTS x 2048 when only the first 2048 rows can hold samples (n_steps <= Nu <= N/PARTS: the
+// reference's production padding -P 3.0, and -P 2.0).  The radix-PARTS first stage then has one variable and PARTS-1 constant
+// inputs, its output blocks are independent 2048-point transforms of values derived from the same 2048 loaded rows, and
+// output k2 = PARTS k' + q of block q lands in row PARTS k' + q.  One CTA per (column tile, q): same tile engine as the 2048
+// case, the first stage folded into the load (for PARTS = 3 the same butterfly values as the generic radix-3 stage on these
+// inputs; the twiddles W^{qp} are read from a table), a 4-D tensor map for the strided rows.
+template <int PARTS>
 __global__ void __launch_bounds__(512, 2)
 fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
                      const uint32_t *__restrict__ n_steps_arr, const float *__restrict__ mean_arr, uint32_t m1, uint32_t m,
-                     const float2 *__restrict__ tw_all, const float2 *__restrict__ tb)
+                     const float2 *__restrict__ tw, const float2 *__restrict__ tb, const float2 *__restrict__ tw_parts)
 {
-    const int third = THIRDS == 3 ? (int)blockIdx.z : -1;
-    // in-tile twiddles of the 2048-point stages: the table of the 6144 plan starts with the 2 x 2048 radix-3 entries
-    const float2 *__restrict__ tw = THIRDS == 3 ? tw_all + 2 * kTmaL : tw_all;
+    const int part = PARTS > 1 ? (int)blockIdx.z : -1;
     constexpr int L = kTmaL, ROWS = kTmaRows, NS = cfg_stages(L), RL = cfg_radix(L, NS - 1);
     static_assert(NS == 3 && RL == 8 && cfg_threads(L) == 512, "written for 2048 = 16 x 16 x 8 with 512 threads");
     extern __shared__ __align__(128) float2 sm[];
@@ -528,7 +529,7 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     }
 
     SmemIO<L, ROWS, 3> io{sm};
-    const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, third, third > 0 ? tw_all + (third - 1) * kTmaL : tw_all};
+    const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, part, PARTS, part > 0 ? tw_parts + (part - 1) * kTmaL : tw_parts};
     tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true>(tw, dload, io);
     __syncthreads();
     tile_middle<L, ROWS, 3, 1, NS - 1>(tw, sm);
@@ -557,7 +558,7 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
         Dft<RL>::run(v[it]);
         const uint32_t col = col0 + rows_[it];
         float sn, cs;
-        const uint32_t k2b = THIRDS == 3 ? 3u * (uint32_t)kb_[it] + (uint32_t)third : (uint32_t)kb_[it];
+        const uint32_t k2b = PARTS > 1 ? (uint32_t)PARTS * (uint32_t)kb_[it] + (uint32_t)part : (uint32_t)kb_[it];
         sincospif(-2.0f * (float)(col * k2b) * inv_m, &sn, &cs);
         const float2 a = make_float2(cs, sn);
         const float2 *__restrict__ t = tb + (size_t)col * RL;
@@ -573,9 +574,9 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int k = 0; k < L / kTmaBox; ++k) {
-            if constexpr (THIRDS == 3)
+            if constexpr (PARTS > 1)
                 asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%1, %2, %3, %4}], [%5];" ::"l"(&out_map),
-                             "r"((int)(2u * col0)), "r"(third), "r"(k * kTmaBox), "r"(b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
+                             "r"((int)(2u * col0)), "r"(part), "r"(k * kTmaBox), "r"(b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
                              : "memory");
             else
                 asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&out_map),
@@ -866,7 +867,7 @@ float2 *upload(const std::vector<float2> &v)
 
 } // namespace
 
-int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
+int brp_fft_plan_create(BrpFftPlan *p, uint32_t n, uint32_t nu_hint)
 {
     memset(p, 0, sizeof(*p));
     if (n < 512 || (n & 1)) return RADPUL_CUDA_FFT_PLAN;
@@ -875,7 +876,14 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
     while ((odd & 1) == 0) { odd >>= 1; ++a; }
     if (odd != 1 && odd != 3) return RADPUL_CUDA_FFT_PLAN; // lengths 2^a and 3*2^a only (like the OpenCL backend)
     // pass 2 length m1 = 2^floor(a/2); pass 1 length m2 = m / m1 carries the factor 3 if there is one
-    const uint32_t m1 = 1u << (a / 2), m2 = m / m1;
+    uint32_t m1 = 1u << (a / 2), m2 = m / m1;
+    // m = 2^22 (n = 2^23) splits 2048 x 2048 by the rule above; when only the first half of the series can hold samples
+    // (padding 2) 1024 x 4096 is better: pass 1 runs as two 2048-row sub-transforms on the tensor-copy engine and pass 2 gets
+    // its fastest shape
+    if (odd == 1 && m2 == 2048 && m1 == 2048 && nu_hint != 0 && nu_hint <= 2u * 1024u * 2048u) {
+        m1 = 1024;
+        m2 = 4096;
+    }
     const TileInfo *t1 = find_tile(m2), *t2 = find_tile(m1);
     if (!t1 || !t2) return RADPUL_CUDA_FFT_PLAN;
     p->n = n; p->m = m; p->m1 = m1; p->m2 = m2; p->radix3 = (odd == 3);
@@ -907,6 +915,27 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n)
         tw[k] = make_float2((float)cos(ang), (float)sin(ang));
     }
     p->tw_untangle_b = upload(tw);
+    p->parts = (m2 % 2048 == 0 && m2 / 2048 >= 1 && m2 / 2048 <= 3) ? (int)(m2 / 2048) : 0;
+    if (p->parts > 1) {
+        tw.resize((size_t)(p->parts - 1) * 2048);
+        for (int q = 1; q < p->parts; ++q)
+            for (uint32_t pos = 0; pos < 2048; ++pos) {
+                const double ang = -2.0 * M_PI * (double)((unsigned long long)q * pos % m2) / (double)m2;
+                tw[(size_t)(q - 1) * 2048 + pos] = make_float2((float)cos(ang), (float)sin(ang));
+            }
+        std::vector<float2> tile2048; // in-tile twiddles of the 2048-point stages, appended behind the W^{qp} rows
+        gen_tile_tw<2048>(tile2048);
+        tw.insert(tw.end(), tile2048.begin(), tile2048.end());
+        p->tw_parts = upload(tw);
+        tw.resize((size_t)m1 * 8);
+        for (uint32_t col = 0; col < m1; ++col)
+            for (int q = 0; q < 8; ++q) {
+                const double ang = -2.0 * M_PI * (double)((unsigned long long)col * q) / ((double)m1 * 8.0);
+                tw[(size_t)col * 8 + q] = make_float2((float)cos(ang), (float)sin(ang));
+            }
+        p->tw_inter_parts = upload(tw);
+        if (!p->tw_parts || !p->tw_inter_parts) p->parts = 0; // fall back to the plain kernel
+    }
     if (!p->tw_pass1 || !p->tw_pass2 || !p->tw_untangle_a || !p->tw_untangle_b || !p->tw_inter_hi) {
         brp_fft_plan_destroy(p);
         return RADPUL_CUDA_MEM_ALLOC_DEVICE;
@@ -931,6 +960,8 @@ void brp_fft_plan_destroy(BrpFftPlan *p)
     cudaFree(p->tw_untangle_b);
     cudaFree(p->tw_inter_hi);
     cudaFree(p->tw_inter_lo);
+    cudaFree(p->tw_parts);
+    cudaFree(p->tw_inter_parts);
     memset(p, 0, sizeof(*p));
 }
 
@@ -969,39 +1000,36 @@ static bool encode_tile_map(tensor_map_encode_fn enc, CUtensorMap *map, const vo
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-// returns 0 (use the plain kernel), 1 (2048-row tiles) or 3 (three 2048-row sub-transforms of a 6144-row pass)
+// returns 0 (use the plain kernel) or the number of 2048-row sub-transforms pass 1 runs as (1, 2 or 3)
 static int pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride, const float2 *work, int batch, uint32_t n_steps_bound,
                           CUtensorMap *in_map, CUtensorMap *out_map)
 {
-    if (p.m1 % kTmaRows != 0) return 0;
-    int thirds = 0;
-    if (p.m2 == (uint32_t)kTmaL) thirds = 1;
-    // 3 x 2048: only valid when no sample can sit beyond row 2048 (a row is 2*m1 samples)
-    else if (p.m2 == 3u * kTmaL && n_steps_bound != 0 && n_steps_bound <= 2u * p.m1 * (uint32_t)kTmaL) thirds = 3;
-    else return 0;
+    if (p.m1 % kTmaRows != 0 || p.parts < 1) return 0;
+    // more than one part: only valid when no sample can sit beyond row 2048 (a row is 2*m1 samples)
+    if (p.parts > 1 && (n_steps_bound == 0 || n_steps_bound > 2u * p.m1 * (uint32_t)kTmaL)) return 0;
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc) return 0;
     static bool configured = false;
     if (!configured) {
-        if (cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 Layout<kTmaL, kTmaRows, 3>::BYTES) != cudaSuccess ||
-            cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 Layout<kTmaL, kTmaRows, 3>::BYTES) != cudaSuccess)
+        const int bytes = Layout<kTmaL, kTmaRows, 3>::BYTES;
+        if (cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess ||
+            cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess ||
+            cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
             return 0;
         configured = true;
     }
     if (!encode_tile_map(enc, in_map, in, p.m1, p.m2, in_stride, batch)) return 0;
-    if (thirds == 1) return encode_tile_map(enc, out_map, work, p.m1, p.m2, 2 * (size_t)p.m, batch) ? 1 : 0;
-    // rows 3 k' + q of the intermediate as [batch][k'][q][2*m1 floats]
+    if (p.parts == 1) return encode_tile_map(enc, out_map, work, p.m1, p.m2, 2 * (size_t)p.m, batch) ? 1 : 0;
+    // rows parts*k' + q of the intermediate as [batch][k'][q][2*m1 floats]
     if ((uintptr_t)work & 15) return 0;
-    const cuuint64_t dims[4] = {2ull * p.m1, 3, (cuuint64_t)kTmaL, (cuuint64_t)batch};
-    const cuuint64_t strides[3] = {8ull * p.m1, 24ull * p.m1, 8ull * p.m};
+    const cuuint64_t dims[4] = {2ull * p.m1, (cuuint64_t)p.parts, (cuuint64_t)kTmaL, (cuuint64_t)batch};
+    const cuuint64_t strides[3] = {8ull * p.m1, 8ull * p.m1 * p.parts, 8ull * p.m};
     const cuuint32_t box[4] = {2 * kTmaRows, 1, kTmaBox, 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     return enc(out_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float2 *>(work), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS
-               ? 3
+               ? p.parts
                : 0;
 }
 
@@ -1037,13 +1065,17 @@ static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, si
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
     CUtensorMap in_map, out_map;
-    const int thirds = pass1_tma_maps(p, in, in_stride, work, batch, n_steps_bound, &in_map, &out_map);
-    if (thirds == 1)
-        fft_pass1_tma_kernel<1><<<g1, 512, Layout<kTmaL, kTmaRows, 3>::BYTES, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1,
-                                                                                  p.tw_inter_hi);
-    else if (thirds == 3)
-        fft_pass1_tma_kernel<3><<<dim3(p.m1 / kTmaRows, batch, 3), 512, Layout<kTmaL, kTmaRows, 3>::BYTES, st>>>(
-            in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
+    const int parts = pass1_tma_maps(p, in, in_stride, work, batch, n_steps_bound, &in_map, &out_map);
+    const int tma_smem = Layout<kTmaL, kTmaRows, 3>::BYTES;
+    const dim3 gp(p.m1 / kTmaRows, batch, parts > 0 ? parts : 1);
+    if (parts == 1)
+        fft_pass1_tma_kernel<1><<<gp, 512, tma_smem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1, p.tw_inter_hi, nullptr);
+    else if (parts == 2) // tw_parts: (parts-1) rows of W^{qp}, then the in-tile twiddles of the 2048-point stages
+        fft_pass1_tma_kernel<2><<<gp, 512, tma_smem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_parts + 1 * kTmaL,
+                                                         p.tw_inter_parts, p.tw_parts);
+    else if (parts == 3)
+        fft_pass1_tma_kernel<3><<<gp, 512, tma_smem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_parts + 2 * kTmaL,
+                                                         p.tw_inter_parts, p.tw_parts);
     else
         t1->p1<<<g1, t1->threads, t1->smem1, st>>>(in, in_stride, n_steps, mean, work, p.m1, p.m, p.tw_pass1, p.tw_inter_hi);
     cudaError_t e = cudaGetLastError();

@@ -144,7 +144,7 @@ int brp_search_create(brp_search **out, int device, const brp_geometry *g, float
     s->max_batch = max_batch;
     rc = brp_base_thresholds(fA, g->fft_size, s->thr.t);
     if (rc) { free(s); return rc; }
-    rc = brp_fft_plan_create(&s->plan, g->nsamples);
+    rc = brp_fft_plan_create(&s->plan, g->nsamples, g->nsamples_unpadded);
     if (rc) { free(s); return rc; }
     s->rs_stride = ((size_t)g->nsamples_unpadded + 3) & ~(size_t)3;
     // the harmonic-summing bulk copies round slices up to 16 bytes; the tensor stores of FFT pass 2 write the last row of
