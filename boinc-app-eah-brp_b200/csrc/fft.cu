@@ -439,6 +439,9 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
 // Lane mappings and padding chosen with tools/pass1_tma_layout.py (all accesses conflict-free except the dense read).
 // Arithmetic is the same as in fft_pass1_kernel (same butterflies, same twiddle construction): results are bit-identical.
 constexpr int kTmaL = 2048, kTmaRows = 4, kTmaBox = 256;
+#ifndef BRP_FFT_L2_PREFETCH
+#define BRP_FFT_L2_PREFETCH 148
+#endif
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -517,6 +520,22 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
                              smem_addr(sm + k * kTmaBox * ROWS)),
                          "l"(&in_map), "r"((int)(2u * col0)), "r"((int)(k * kTmaBox)), "r"(b), "r"(bar_a)
                          : "memory");
+#if BRP_FFT_L2_PREFETCH > 0
+        // pull the input tile of a CTA that starts about half a resident wave later into L2 (measured: pass 1 2.4 % faster at a
+        // distance of 148 tiles, nothing at 296, slower beyond)
+        {
+            const uint32_t ahead = (blockIdx.y * gridDim.x + blockIdx.x) + BRP_FFT_L2_PREFETCH;
+            const uint32_t by = ahead / gridDim.x, bx = ahead - by * gridDim.x;
+            if (by < gridDim.y) {
+                const uint32_t ns2 = n_steps_arr[by];
+                const uint32_t need2 = min((uint32_t)L, (ns2 + 2u * m1 - 1u) / (2u * m1));
+                for (uint32_t k = 0; k * kTmaBox < need2; ++k)
+                    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(&in_map),
+                                 "r"((int)(2u * bx * ROWS)), "r"((int)(k * kTmaBox)), "r"((int)by)
+                                 : "memory");
+            }
+        }
+#endif
     }
     __syncthreads();
     {
