@@ -25,8 +25,10 @@
 // whole batch with a two-deep ring; a producer warp issues the copies of tile t+1 while four consumer warps sum
 // tile t (eight bins per thread), stages handed over through full/empty mbarriers without any block-wide barrier.
 // Measured on B200 (tools/hs_sweep.sh): 2 stages x 1024 bins x 4 consumer warps, three CTAs per SM, is the fastest
-// shape (77 us per 16 templates = 12.4 TB/s out of L2, the L2 -> SM limit); deeper rings or wider CTAs lose more
-// to the lower CTA count than they gain in prefetch distance.
+// shape (77 us per 16 templates); deeper rings or wider CTAs lose more to the lower CTA count than they gain in
+// prefetch distance.  What bounds the kernel is shared-memory bandwidth: 16 x 4 bytes read per bin by the consumers
+// (80 B/clk/SM) plus the 8.5*H floats per template written by the bulk copies (43 B/clk/SM) against 128 B/clk/SM;
+// halving the bytes copied (probe: odd harmonics not fetched) shortens it by only 7 %.
 // Because i0 is a multiple of 1024, (l*i0+8)>>4 = l*i0/16 exactly, and the position of bin i0+tid+128*r inside
 // slice l is ((l*tid+8)>>4) + 8*l*r: a per-thread constant plus a compile-time offset.  The hot loop therefore
 // has no index arithmetic at all; consecutive lanes read consecutive or identical shared-memory words
