@@ -29,7 +29,7 @@ __device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta
 
 template <int W, bool STORE>
 __global__ void __launch_bounds__(256) probe(const __grid_constant__ CUtensorMap src, const __grid_constant__ CUtensorMap dst,
-                                             int tiles_per_template, int n_tiles, float *sink)
+                                             int tiles_per_template, int n_tiles, float *sink, int store_shift)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) unsigned long long bar;
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(256) probe(const __grid_constant__ CUtensorMap
             if (threadIdx.x == 0) {
 #pragma unroll
                 for (int k = 0; k < ROWS / BOX_ROWS; ++k)
-                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&dst), "r"(c0),
+                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&dst), "r"(c0 + store_shift),
                                  "r"(r0 + k * BOX_ROWS), "r"(s32(smem + (size_t)k * BOX_ROWS * W * 8))
                                  : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -99,7 +99,7 @@ static CUtensorMap make_map(EncodeFn enc, void *base, int w)
 }
 
 template <int W, bool STORE>
-static void run(EncodeFn enc, float *a, float *b, float *sink, int ctas_per_sm)
+static void run(EncodeFn enc, float *a, float *b, float *sink, int ctas_per_sm, int store_shift = 0)
 {
     CUtensorMap ma = make_map(enc, a, W), mb = make_map(enc, b, W);
     const int smem = ROWS * W * 8;
@@ -109,18 +109,18 @@ static void run(EncodeFn enc, float *a, float *b, float *sink, int ctas_per_sm)
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    for (int i = 0; i < 3; i++) probe<W, STORE><<<grid, 256, smem>>>(ma, mb, tiles_per_template, n_tiles, sink);
+    for (int i = 0; i < 3; i++) probe<W, STORE><<<grid, 256, smem>>>(ma, mb, tiles_per_template, n_tiles, sink, store_shift);
     CK(cudaDeviceSynchronize());
     const int reps = 20;
     CK(cudaEventRecord(e0));
-    for (int i = 0; i < reps; i++) probe<W, STORE><<<grid, 256, smem>>>(ma, mb, tiles_per_template, n_tiles, sink);
+    for (int i = 0; i < reps; i++) probe<W, STORE><<<grid, 256, smem>>>(ma, mb, tiles_per_template, n_tiles, sink, store_shift);
     CK(cudaEventRecord(e1));
     CK(cudaDeviceSynchronize());
     float ms;
     CK(cudaEventElapsedTime(&ms, e0, e1));
     const double us = 1e3 * ms / reps, bytes = (double)ROWS * COLS * 8 * BATCH * (STORE ? 2 : 1);
-    printf("W=%2d columns (%3d-byte runs) %s, %d CTA/SM: %7.1f us per 16-template volume, %6.0f GB/s\n", W, W * 8,
-           STORE ? "load+store" : "load only ", ctas_per_sm, us, bytes / us * 1e-3);
+    printf("W=%2d columns (%3d-byte runs) %s, %d CTA/SM, store shifted by %d floats: %7.1f us per 16-template volume, %6.0f GB/s (%s)\n", W,
+           W * 8, STORE ? "load+store" : "load only ", ctas_per_sm, store_shift, us, bytes / us * 1e-3, cudaGetErrorString(cudaGetLastError()));
 }
 
 int main()
@@ -141,6 +141,7 @@ int main()
     run<4, true>(enc, a, b, sink, 3);
     run<2, false>(enc, a, b, sink, 4);
     run<2, true>(enc, a, b, sink, 4);
+    run<2, true>(enc, a, b, sink, 4, 1);   // is a store that starts 4 bytes past a 16-byte boundary legal?
     run<8, false>(enc, a, b, sink, 1);
     run<8, true>(enc, a, b, sink, 1);
     return 0;
