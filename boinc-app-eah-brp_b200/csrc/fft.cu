@@ -1028,7 +1028,10 @@ static int pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride
     if (p.parts > 1 && (n_steps_bound == 0 || n_steps_bound > 2u * p.m1 * (uint32_t)kTmaL)) return 0;
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc) return 0;
-    static bool configured = false;
+    static bool configured_on[64]; // function attributes are per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    bool &configured = configured_on[(dev >= 0 && dev < 64) ? dev : 0];
     if (!configured) {
         const int bytes = Layout<kTmaL, kTmaRows, 3>::BYTES;
         if (cudaFuncSetAttribute((const void *)fft_pass1_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess ||
@@ -1062,7 +1065,10 @@ static bool pass2_tma_map(const BrpFftPlan &p, const float *out, size_t out_stri
     if ((size_t)rows * p.m2 > out_stride || (out_stride & 3) || ((uintptr_t)out & 15)) return false;
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc) return false;
-    static bool configured = false;
+    static bool configured_on[64]; // function attributes are per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    bool &configured = configured_on[(dev >= 0 && dev < 64) ? dev : 0];
     if (!configured) {
         if (cudaFuncSetAttribute((const void *)fft_pass2_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  Layout<1024, 8, 2>::BYTES) != cudaSuccess)
