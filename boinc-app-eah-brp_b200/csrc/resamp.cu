@@ -63,7 +63,7 @@ static_assert(kGroupLen == 16 && 128 % kGroupLen == 0, "the lane mapping below a
 // A block walks kChunks chunks: the block-level epilogue (reduction, fence, atomic) is a serial chain of a few
 // microseconds, and with one chunk per block that chain, not bandwidth or issue slots, set the kernel's duration.
 constexpr int kChunks = 4;
-constexpr uint32_t kBlockSpan = (uint32_t)kChunks * BRP_RESAMP_SAMPLES_PER_BLOCK;
+constexpr uint32_t kBlockSpan = (uint32_t)kChunks * BRP_RESAMP_SAMPLES_PER_BLOCK; // 8 warps x kChunks segments of 512
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -177,12 +177,19 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
         }
     };
 
+    // A warp owns kChunks consecutive segments of 512 samples; in round r lane l handles the four samples at 128 r + 4 l.
+    // One timing-model evaluation per group of kGroupLen samples (lane l: group l of the segment).  The right end of a
+    // group is its neighbour's left end, fetched by shuffle; the right end of the segment's last group is lane 0's
+    // evaluation for the NEXT segment, which is computed one iteration ahead.  No shared memory, no block barrier.
+    const uint32_t warp_lo = block_lo + (uint32_t)warp * (kChunks * 32 * kGroupLen);
+    float d_next = 0.0f;
+    int cell_next = 0;
+    if (MODE == 2 && runs_ok && warp_lo < n_steps)
+        d_next = brp_del_t_cell((float)(warp_lo + (uint32_t)lane * kGroupLen), tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, cell_next);
 #pragma unroll 1
     for (int chunk = 0; chunk < kChunks; ++chunk) {
-        const uint32_t chunk_lo = block_lo + (uint32_t)chunk * BRP_RESAMP_SAMPLES_PER_BLOCK;
-        if (chunk_lo >= n_steps) break; // uniform
-        // a warp owns 512 consecutive samples of the chunk; in round r lane l handles the four samples at 128 r + 4 l
-        const uint32_t seg_lo = chunk_lo + (uint32_t)warp * (32 * kGroupLen);
+        const uint32_t seg_lo = warp_lo + (uint32_t)chunk * (32 * kGroupLen);
+        if (seg_lo >= n_steps) break; // uniform within the warp
         if (MODE != 2 || !runs_ok) {
 #pragma unroll
             for (int r = 0; r < kGroupLen / 4; ++r) {
@@ -196,20 +203,18 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
             continue;
         }
         if constexpr (MODE == 2) {
-            // one evaluation per group of kGroupLen samples (lane l: group l of the warp's segment); the right end of a
-            // group is its neighbour's left end, fetched by shuffle.  The right end of the warp's last group is evaluated
-            // by the warp itself (one more pass with one active lane) rather than fetched from the next warp through
-            // shared memory: no block barrier, warps run independently.
             const uint32_t g_lo = seg_lo + (uint32_t)lane * kGroupLen;
-            int cell;
-            const float d_own = brp_del_t_cell((float)g_lo, tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, cell);
+            const float d_own = d_next;
+            const int cell = cell_next;
+            d_next = brp_del_t_cell((float)(g_lo + 32 * kGroupLen), tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, cell_next);
             float2 eb;
             eb.x = __shfl_down_sync(0xffffffffu, d_own, 1);
             eb.y = __int_as_float(__shfl_down_sync(0xffffffffu, cell, 1));
+            const float d_first = __shfl_sync(0xffffffffu, d_next, 0);
+            const int cell_first = __shfl_sync(0xffffffffu, cell_next, 0);
             if (lane == 31) {
-                int c2;
-                eb.x = brp_del_t_cell((float)(g_lo + kGroupLen), tp.tau, tp.Omega, tp.Psi0, tp.S0, g.dt, g.step_inv, tab, c2);
-                eb.y = __int_as_float(c2);
+                eb.x = d_first;
+                eb.y = __int_as_float(cell_first);
             }
             const float base = (float)g_lo;
             const float lo = __fsub_rn(fminf(d_own, eb.x), eta), hi = __fadd_rn(fmaxf(d_own, eb.x), eta);
@@ -219,6 +224,32 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
             const bool proven = cell == __float_as_int(eb.y) && ka == kb && a >= 1.0f &&
                                 ((__float_as_int(a) ^ __float_as_int(z)) & 0x7F800000) == 0;
             const int verdict = proven ? ka : -1; // index of the group's first sample, or "evaluate every sample"
+            // Most segments (no shift change among their 512 samples) are a plain copy displaced by one warp-uniform shift:
+            // pointers and the alignment case are then computed once per segment instead of once per four samples.
+            const int sh = verdict - (int)g_lo, sh0 = __shfl_sync(0xffffffffu, sh, 0);
+            const int k_seg = (int)seg_lo + sh0;
+            const bool whole = seg_lo + 32u * kGroupLen <= n_steps && k_seg >= 0 && (uint32_t)k_seg + 32u * kGroupLen + 4u <= nu;
+            if (__all_sync(0xffffffffu, verdict >= 0 && sh == sh0) && whole) {
+                const float4 *s4 = reinterpret_cast<const float4 *>(series + (k_seg & ~3)) + lane;
+                float4 *o4 = reinterpret_cast<float4 *>(orow + seg_lo) + lane;
+                const int al = k_seg & 3;
+#pragma unroll
+                for (int r = 0; r < kGroupLen / 4; ++r) {
+                    const float4 q0 = __ldg(s4 + 32 * r), q1 = __ldg(s4 + 32 * r + 1);
+                    float4 o;
+                    if (al == 0) o = q0;
+                    else if (al == 1) o = make_float4(q0.y, q0.z, q0.w, q1.x);
+                    else if (al == 2) o = make_float4(q0.z, q0.w, q1.x, q1.y);
+                    else o = make_float4(q0.w, q1.x, q1.y, q1.z);
+                    o4[32 * r] = o;
+                    acc += (double)((o.x + o.y) + (o.z + o.w));
+                    if (WRITE_IDX) {
+                        const int k = k_seg + 128 * r + 4 * lane;
+                        *reinterpret_cast<int4 *>(irow + seg_lo + 128u * r + 4u * lane) = make_int4(k, k + 1, k + 2, k + 3);
+                    }
+                }
+                continue;
+            }
 #pragma unroll
             for (int r = 0; r < kGroupLen / 4; ++r) {
                 const int src = r * (128 / kGroupLen) + lane / (kGroupLen / 4);
