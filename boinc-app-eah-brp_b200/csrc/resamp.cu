@@ -17,7 +17,7 @@
 //     mean for i >= n_steps on load.  The legacy entry point asks for it to be written (fill_padding).
 //
 // Run detection (MODE 2, the production path).  The shift idx(i) - i changes once per ~1000 samples only, so the
-// timing model is evaluated at every FOURTH sample (one per thread and group of four) and the three samples in
+// timing model is evaluated at every 16th sample (one per lane and group of sixteen) and the fifteen samples in
 // between are proven, not computed:
 //   (1) G(i, x) = (int)(fl(i - x) + 0.5) is non-increasing in x (float subtraction and the rounding are monotone), so
 //       lo <= del_t[i] <= hi  and  G(i, lo) == G(i, hi)  pin idx(i) without evaluating del_t[i];
@@ -30,13 +30,15 @@
 //       derivative changes sign the excursion is below 1e-10).  What is not monotone is the rounding of the seven
 //       operations behind d: at most 7e-7 * |tau|*step_inv per value.  eta = 2.5e-6*|tau|*step_inv + 1e-6 covers the
 //       three values involved with room to spare.
-// A group falls back to evaluating all four samples when its ends lie in different table cells, when the two
-// bounds of (1) disagree (a shift change may lie inside), when i - x crosses a binade or is below 1.  The tests
+// A group falls back to evaluating all of its samples when its ends lie in different table cells, when the two
+// bounds of (1) disagree (a shift change may lie inside), when i - x crosses a binade or is below 1.  A warp owns 512
+// consecutive samples per step; when all 32 groups are proven with the same shift (about 60 % of the steps) the step is a
+// plain displaced copy with one alignment case for the whole warp.  The tests
 // compare the index arrays with the oracle bit for bit, and brp_stage_resample_compare() checks MODE 2 against MODE 1
 // sample by sample on the device for whole banks.
 //
-// grid = (ceil(Nu/16384), batch), block = 256, four chunks of 4096 samples per block.  HBM-bound: 4*Nu read (L2-resident across the batch) +
-// 4*n_steps written per template.
+// grid = (ceil(Nu/16384), batch), block = 256: a warp walks four adjacent 512-sample segments.  HBM traffic: 4*Nu read
+// (L2-resident across the batch) + 4*n_steps written per template.
 #include "brp_device.cuh"
 #include "brp_internal.h"
 
