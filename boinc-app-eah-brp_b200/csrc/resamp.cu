@@ -90,7 +90,7 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
     __shared__ float2 s_tab[65];
     __shared__ int s_nsteps;
     __shared__ double s_warp[BRP_RESAMP_THREADS / 32];
-    __shared__ bool s_last;
+    __shared__ unsigned int s_arrived;
 
     const int b = blockIdx.y;
     const uint32_t nblk = gridDim.x;
@@ -99,7 +99,10 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
     const uint32_t nu = g.nu;
 
     if (threadIdx.x < 65) s_tab[threadIdx.x] = c_brp_sincos[threadIdx.x];
-    if (threadIdx.x == 0) s_nsteps = -1;
+    if (threadIdx.x == 0) {
+        s_nsteps = -1;
+        s_arrived = 0u;
+    }
     __syncthreads();
     const SmemTable tab{s_tab};
 
@@ -287,35 +290,36 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
         }
     } // chunks
 
-    // ---- mean: fixed-order block reduction, per-block partials, last block of the template finishes
+    // ---- mean: fixed-order reduction.  Warp sums -> block partial (by whichever warp of the block finishes last) ->
+    // template total (by whichever block finishes last).  The order of every sum is fixed by index, never by arrival, so
+    // the mean does not depend on scheduling; no block-wide barrier: warps that are done leave.
     acc = warp_sum(acc);
-    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
+    int last_warp = 0;
+    if (lane == 0) {
+        s_warp[warp] = acc;
+        __threadfence(); // this warp's global stores (the series, n_steps) and its sum before the arrival is counted
+        last_warp = atomicAdd(&s_arrived, 1u) == BRP_RESAMP_THREADS / 32 - 1;
+    }
+    if (!__shfl_sync(0xffffffffu, last_warp, 0)) return;
+    int last_block = 0;
+    if (lane == 0) {
+        __threadfence_block();
         double t = 0.0;
 #pragma unroll
-        for (int w = 0; w < BRP_RESAMP_THREADS / 32; ++w) t += s_warp[w];
+        for (int w = 0; w < BRP_RESAMP_THREADS / 32; ++w) t += ((volatile double *)s_warp)[w];
         partials[(size_t)b * nblk + blockIdx.x] = t;
         __threadfence();
-        const uint32_t done = atomicAdd(&counters[b], 1u);
-        s_last = (done == nblk - 1);
+        last_block = atomicAdd(&counters[b], 1u) == nblk - 1;
     }
-    __syncthreads();
-    if (!s_last) return;
+    if (!__shfl_sync(0xffffffffu, last_block, 0)) return;
     __threadfence();
     double t = 0.0;
-    for (uint32_t k = threadIdx.x; k < nblk; k += BRP_RESAMP_THREADS) t += __ldcg(&partials[(size_t)b * nblk + k]);
+    for (uint32_t k = lane; k < nblk; k += 32) t += __ldcg(&partials[(size_t)b * nblk + k]);
     t = warp_sum(t);
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = t;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double tot = 0.0;
-#pragma unroll
-        for (int w = 0; w < BRP_RESAMP_THREADS / 32; ++w) tot += s_warp[w];
+    if (lane == 0) {
         const uint32_t ns = __ldcg(&n_steps_out[b]);
-        mean_out[b] = (float)(tot / (double)ns); // mean /= (float)n_steps  (:125)
-        counters[b] = 0u;                        // ready for the next launch
+        mean_out[b] = (float)(t / (double)ns); // mean /= (float)n_steps  (:125)
+        counters[b] = 0u;                      // ready for the next launch
     }
 }
 
