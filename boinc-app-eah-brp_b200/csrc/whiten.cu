@@ -12,8 +12,7 @@
 // zap list is not supported (the caller gets RADPUL_EVAL and can fall back to an unzapped search).
 //
 // The median is exact (same order statistics as rngmed.c, even windows average the two middle values in
-// double like rngmed.c:179,329): every output bin selects its k-th smallest window value by bisection on the
-// bit pattern of the non-negative floats, with the window staged in shared memory.
+// double like rngmed.c:179,329): see running_median_kernel.
 #include <math.h>
 #include <stdio.h>
 
@@ -32,14 +31,44 @@ __global__ void periodogram_kernel(const float2 *__restrict__ X, float *__restri
     ps[i] = i == 0 ? 0.0f : (float)((double)v.x * (double)v.x + (double)v.y * (double)v.y);
 }
 
+// Running median.  A thread produces kMedRun consecutive outputs.  The first one selects the k-th smallest value of its
+// window by bisection on the bit pattern of the non-negative floats (31 passes over the window).  Every further window
+// differs from the previous one by one element out and one in, so the rank of the previous median moves by at most one:
+// ONE pass that counts the values below / not above the previous median and finds its nearest neighbours on either side
+// decides between "same value", "predecessor" and "successor".  An even window needs the (k+1)-th value too: one more pass
+// relative to the new k-th value.  About 3.9 passes per output instead of 32, same order statistics.
+// The window lives in shared memory; a thread's windows start kMedRun words apart, so each lane walks its window from a
+// different offset (lane t starts at element t and wraps around): the 32 addresses of a warp then fall into 32 different banks.
+constexpr int kMedRun = 16;
+
+struct MedScan {
+    int lt, le;        // values < pivot, values <= pivot
+    uint32_t pred, succ; // largest value < pivot (0 if none), smallest value > pivot (+inf pattern if none)
+};
+
+__device__ __forceinline__ MedScan med_scan(const uint32_t *__restrict__ win, int n, int skew, uint32_t pivot)
+{
+    MedScan r{0, 0, 0u, 0x7F800000u};
+    auto visit = [&](uint32_t v) {
+        r.lt += (v < pivot);
+        r.le += (v <= pivot);
+        if (v < pivot) r.pred = max(r.pred, v);
+        if (v > pivot) r.succ = min(r.succ, v);
+    };
+    for (int j = skew; j < n; ++j) visit(win[j]);
+    for (int j = skew - 1; j >= 0; --j) visit(win[j]); // downwards: lane t reads word 17 t - 1 - step, again one bank per lane
+    return r;
+}
+
 // k-th smallest (0-based) of win[0..n) for non-negative floats: bisection on the bit pattern
-__device__ __forceinline__ uint32_t select_kth(const uint32_t *__restrict__ win, int n, int k)
+__device__ __forceinline__ uint32_t select_kth(const uint32_t *__restrict__ win, int n, int k, int skew)
 {
     uint32_t x = 0;
     for (int bit = 30; bit >= 0; --bit) {
         const uint32_t cand = x | (1u << bit);
         int cnt = 0;
-        for (int j = 0; j < n; ++j) cnt += (win[j] < cand);
+        for (int j = skew; j < n; ++j) cnt += (win[j] < cand);
+        for (int j = skew - 1; j >= 0; --j) cnt += (win[j] < cand);
         if (cnt <= k) x = cand;
     }
     return x;
@@ -48,34 +77,38 @@ __device__ __forceinline__ uint32_t select_kth(const uint32_t *__restrict__ win,
 __global__ void __launch_bounds__(kMedThreads)
 running_median_kernel(const float *__restrict__ ps, uint32_t length, uint32_t bsize, float *__restrict__ med, uint32_t n_out)
 {
-    extern __shared__ uint32_t sw[]; // kMedThreads + bsize - 1 values as bit patterns
-    const uint32_t first = blockIdx.x * kMedThreads;
-    const uint32_t span = kMedThreads + bsize - 1;
+    extern __shared__ uint32_t sw[]; // kMedThreads*kMedRun + bsize - 1 values as bit patterns
+    const uint32_t first = blockIdx.x * (kMedThreads * kMedRun);
+    const uint32_t span = kMedThreads * kMedRun + bsize - 1;
     for (uint32_t j = threadIdx.x; j < span; j += kMedThreads) {
         const uint32_t src = first + j;
         sw[j] = src < length ? __float_as_uint(ps[src]) : 0x7F800000u; // +inf beyond the end (never selected)
     }
     __syncthreads();
-    const uint32_t i = first + threadIdx.x;
-    if (i >= n_out) return;
-    const uint32_t *win = sw + threadIdx.x; // consecutive threads read consecutive words: conflict-free
+    const int n = (int)bsize;
     const int mid = (int)((bsize + (bsize & 1u)) / 2u) - 1; // rngmed.c:104
-    const uint32_t a = select_kth(win, (int)bsize, mid);
-    if (bsize & 1u) {
-        med[i] = __uint_as_float(a);
-        return;
+    const int skew = min((int)(threadIdx.x & 31), n - 1);
+    uint32_t a = 0;
+    for (int r = 0; r < kMedRun; ++r) {
+        const uint32_t i = first + threadIdx.x * kMedRun + r;
+        if (i >= n_out) return;
+        const uint32_t *win = sw + threadIdx.x * kMedRun + r;
+        if (r == 0) {
+            a = select_kth(win, n, mid, skew);
+        } else {
+            const MedScan s = med_scan(win, n, skew, a); // a = k-th value of the previous window
+            if (mid < s.lt) a = s.pred;                  // rank moved up by one: the k-th value is the predecessor
+            else if (mid >= s.le) a = s.succ;            // rank moved down by one (or the old median left the window)
+        }
+        if (bsize & 1u) {
+            med[i] = __uint_as_float(a);
+            continue;
+        }
+        // even window: the next order statistic is a itself if it occurs again above rank mid, else the smallest value > a
+        const MedScan s2 = med_scan(win, n, skew, a);
+        const uint32_t bb = (s2.le >= mid + 2) ? a : s2.succ;
+        med[i] = (float)((double)(__uint_as_float(a) + __uint_as_float(bb)) / 2.0); // float add, double halving (rngmed.c:179)
     }
-    // even window: the next order statistic is a itself if it occurs more than once above rank mid, else the
-    // smallest value greater than a
-    int le = 0;
-    uint32_t nxt = 0x7F800000u;
-    for (uint32_t j = 0; j < bsize; ++j) {
-        const uint32_t v = win[j];
-        le += (v <= a);
-        if (v > a && v < nxt) nxt = v;
-    }
-    const uint32_t bb = (le >= mid + 2) ? a : nxt;
-    med[i] = (float)((double)(__uint_as_float(a) + __uint_as_float(bb)) / 2.0); // float add, double halving (rngmed.c:179)
 }
 
 // steps 4 and the zeroing of step 6
@@ -157,7 +190,7 @@ extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_un
         const uint32_t ns_host[2] = {nu, n};
         const float zero = 0.0f;
         const size_t nu4 = ((size_t)nu + 3) & ~(size_t)3;
-        const int med_smem = (int)((kMedThreads + window - 1) * sizeof(uint32_t));
+        const int med_smem = (int)((kMedThreads * kMedRun + window - 1) * sizeof(uint32_t));
         WH_TRY(cudaMalloc((void **)&d_x, sizeof(float) * nu4), RADPUL_CUDA_MEM_ALLOC_DEVICE);
         WH_TRY(cudaMalloc((void **)&d_X, sizeof(float2) * ((size_t)m + 2)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
         WH_TRY(cudaMalloc((void **)&d_zc, sizeof(float2) * (size_t)m), RADPUL_CUDA_MEM_ALLOC_DEVICE);
@@ -180,7 +213,7 @@ extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_un
         WH_TRY(brp_launch_fft_spectrum(plan, d_x, d_ns, d_mean, d_work, d_X, m + 1, st), RADPUL_CUDA_FFT_EXEC);
         // 2.-4. periodogram, running median, rescale, zero the edges
         periodogram_kernel<<<(f + 255) / 256, 256, 0, st>>>(d_X, d_ps, f);
-        running_median_kernel<<<(white_size + kMedThreads - 1) / kMedThreads, kMedThreads, med_smem, st>>>(d_ps, f, window, d_med, white_size);
+        running_median_kernel<<<(white_size + kMedThreads * kMedRun - 1) / (kMedThreads * kMedRun), kMedThreads, med_smem, st>>>(d_ps, f, window, d_med, white_size);
         scale_and_edge_kernel<<<(f + 255) / 256, 256, 0, st>>>(d_X, d_med, f, window_2, white_size);
         // 6. backward transform and renormalisation: 1/sqrt((float)N) held in a float (:1066)
         inverse_prep_kernel<<<(m + 255) / 256, 256, 0, st>>>(d_X, d_zc, m, 2.0f / (float)n);
