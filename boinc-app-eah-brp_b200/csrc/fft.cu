@@ -240,7 +240,7 @@ enum { MAP_ROW_FAST = 0, MAP_BF_FAST = 1 };
 //     auto c = io.begin(row, base);   io.get(c, off);   io.put(c, off, q, value);
 // where base = blk*n + p is the butterfly's first position and off = j*S is a compile-time constant after
 // unrolling, so all per-element address arithmetic folds into immediates.
-template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, typename Load, typename Store>
+template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, bool TREE = false, typename Load, typename Store>
 __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store)
 {
     constexpr int R = cfg_radix(L, STAGE);
@@ -278,7 +278,7 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
         Dft<R>::run(v);
         const auto sc = store.begin(row, base);
         const float2 *__restrict__ twp = tw + TWO + p;
-        if constexpr (!LAST && MAP == MAP_ROW_FAST && ROWS > 1) {
+        if constexpr (!LAST && ((MAP == MAP_ROW_FAST && ROWS > 1) || TREE)) {
             // Row-fast lanes share p between the ROWS rows, so table loads would fetch every twiddle ROWS times
             // (measured: 0.17 L1 wavefronts per element in pass 1).  Load W_n^p once and square/multiply up to
             // W_n^{p q}: the product tree is at most log2(R) deep, i.e. a few ulp.
@@ -325,7 +325,7 @@ __device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm)
 {
     if constexpr (STAGE < END) {
         SmemIO<L, ROWS, PASS> io{sm};
-        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false>(tw, io, io);
+        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false>(tw, io, io); // (a power tree here is slower: measured 257 vs 250 us)
         __syncthreads();
         tile_middle<L, ROWS, PASS, STAGE + 1, END>(tw, sm);
     }
@@ -439,6 +439,9 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
 // Lane mappings and padding chosen with tools/pass1_tma_layout.py (all accesses conflict-free except the dense read).
 // Arithmetic is the same as in fft_pass1_kernel (same butterflies, same twiddle construction): results are bit-identical.
 constexpr int kTmaL = 2048, kTmaRows = 4, kTmaBox = 256;
+#ifndef BRP_FFT_PASS2_TREE
+#define BRP_FFT_PASS2_TREE 1
+#endif
 #ifndef BRP_FFT_L2_PREFETCH
 #define BRP_FFT_L2_PREFETCH 148
 #endif
@@ -646,7 +649,11 @@ __device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, floa
     SmemIO<L, ROWS, 2> io{sm};
     const Pass2Load<L, ROWS> gload{work + (size_t)b * m, a, m2};
 
-    tile_stage<L, ROWS, 0, MAP_BF_FAST, false>(tw, gload, io);
+    // twiddles W^{pq} of this stage by a power tree from W^p: the table loads were a seventh of the kernel's L1 traffic
+    // (measured: 203 -> 191 us per 32 templates)
+    // (only for the power spectrum of the search: the whitening modes keep the double-rounded table twiddles, the tree's
+    // few-ulp twiddle error doubles the error of the whitened series)
+    tile_stage<L, ROWS, 0, MAP_BF_FAST, false, false, (BRP_FFT_PASS2_TREE != 0 && MODE == PASS2_POWER)>(tw, gload, io);
     __syncthreads();
     tile_middle<L, ROWS, 2, 1, NS>(tw, sm);
 
