@@ -318,7 +318,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=int(os.environ.get("BRP_BATCH", "32")))
+    ap.add_argument("--batch", type=int, default=int(os.environ.get("BRP_BATCH", "64")))
     ap.add_argument("--templates", type=int, default=6662)
     ap.add_argument("--log2n", type=int, default=22)
     ap.add_argument("--padding", type=float, default=1.0)

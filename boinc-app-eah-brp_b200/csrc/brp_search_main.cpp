@@ -28,7 +28,7 @@ struct Options {
     unsigned chunk = 2048;            /* templates per brp_search_run between checkpoint opportunities */
     double checkpoint_period_s = 60;  /* wall-clock seconds between checkpoints (0 = after every chunk) */
     long max_templates = -1;          /* stop (with a checkpoint) after this many templates of this invocation */
-    unsigned batch = 32;              /* templates per kernel launch */
+    unsigned batch = 64;              /* templates per kernel launch */
 };
 
 void usage(const char *argv0)
@@ -47,7 +47,7 @@ void usage(const char *argv0)
            " -D, --device           int     CUDA device (default 0)\n"
            " -z, --debug                    more output\n"
            "     --chunk            int     templates per enqueue between checkpoint opportunities (default 2048)\n"
-           "     --batch            int     templates per kernel launch (default 32)\n"
+           "     --batch            int     templates per kernel launch (default 64)\n"
            "     --checkpoint_period float  seconds between checkpoints (default 60; 0 = every chunk)\n"
            "     --max_templates    int     stop after this many templates, leaving a checkpoint\n",
            argv0);
