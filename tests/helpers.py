@@ -38,6 +38,8 @@ def power_close(a, b, rtol=1e-4):
     """|a-b| <= rtol * max(|b|, <P>) (SURVEY.md 8c tap 2: chi^2 bins can be arbitrarily close to 0, hence the floor)."""
     a = np.asarray(a, np.float64)
     b = np.asarray(b, np.float64)
+    if b.size == 0:
+        return 0.0, np.zeros(0)
     floor = max(float(np.mean(np.abs(b))), 1e-30)
     err = np.abs(a - b) / np.maximum(np.abs(b), floor)
     return float(err.max(initial=0.0)), err
