@@ -92,3 +92,27 @@ def test_cli_error_paths(wu):
     assert r.returncode == brp_b200.RADPUL_EFILE
     r = subprocess.run([str(EXE), "-P", "0.5"], capture_output=True, text=True)
     assert r.returncode == brp_b200.RADPUL_EVAL
+
+
+def test_cli_full_size_production_options_equal_the_api_path(tmp_path):
+    """A 2^22-sample work-unit with the production options (-P 3.0 -W, tensor-copy FFT kernels, sub-transform pass 1): the
+    driver's candidate file must be the one the same library calls give when made one by one from Python."""
+    nu = 1 << 22
+    series, q = synth.make_series(nu, seed=31, pulsar=synth.Pulsar(summed_power=400.0))
+    bank = synth.make_bank(96, seed=32)
+    synth.write_binary_wu(tmp_path / "wu.binary", q)
+    synth.write_bank(tmp_path / "bank.txt", bank)
+    (tmp_path / "zap.txt").write_text("")
+    r = subprocess.run([str(EXE), "-i", str(tmp_path / "wu.binary"), "-o", str(tmp_path / "out.cand"), "-t", str(tmp_path / "bank.txt"),
+                        "-l", str(tmp_path / "zap.txt"), "-f", "400", "-A", "0.08", "-P", "3.0", "-W", "-B", "1000", "-D", "0"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = (tmp_path / "out.cand").read_text()
+    wu_series, ts = brp_b200.wu_read(tmp_path / "wu.binary")
+    assert wu_series.size == nu
+    g = brp_b200.derive_geometry(nu, ts, 3.0, 400.0, 1000)
+    white, _ = brp_b200.whiten_series(wu_series, 3.0, 1000)
+    cands, tidx = brp_b200.search_bank(white, g, synth.read_bank(tmp_path / "bank.txt"), fA=0.08, max_batch=64)
+    fin, _ = brp_b200.finalize_candidates(cands, tidx)
+    want = brp_b200.format_candidates(fin, g, ts)
+    assert got == want and got.endswith("%DONE%\n") and got.count("\n") > 5
