@@ -699,6 +699,7 @@ __device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, floa
             const uint32_t k0 = k2 + m2 * (uint32_t)k10;
             float *Pk = P + k0, *Pm = P + (m - k0);
             const uint32_t step = (uint32_t)KSTEP * m2;
+            const float qnorm = 0.25f * norm;
             if constexpr (TMA_OUT) {
                 static_assert(L == 1024 && ROWS == 8 && ITERS == 16 && CPOS == 2 && KSTEP == 64, "staging image below is written for this shape");
                 // The 16-byte runs of this tile's outputs (four consecutive k2 per k1) cost one L1 tag lookup each when stored by
@@ -716,15 +717,15 @@ __device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, floa
                 float *stage_a = reinterpret_cast<float *>(sm); // 1024 x 4 floats
 #pragma unroll
                 for (int it = 0; it < 16; ++it) {
-                    const float2 e = make_float2(0.5f * (za[it].x + zb[it].x), 0.5f * (za[it].y - zb[it].y));
-                    const float2 d = make_float2(0.5f * (za[it].x - zb[it].x), 0.5f * (za[it].y + zb[it].y));
-                    const float2 o = make_float2(d.y, -d.x);
+                    // 2E, 2O and the factor 1/4 moved into norm: scaling by powers of two is exact, the powers are unchanged
+                    const float2 e = make_float2(za[it].x + zb[it].x, za[it].y - zb[it].y);
+                    const float2 o = make_float2(za[it].y + zb[it].y, zb[it].x - za[it].x);
                     const float2 w = cmul(wa, __ldg(twb + 64 * it));
                     const float2 wo = cmul(w, o);
                     const float2 xp = cadd(e, wo), xm = csub(e, wo);
-                    stage_a[4 * (k10 + 64 * it) + r] = norm * fmaf(xp.x, xp.x, xp.y * xp.y);
+                    stage_a[4 * (k10 + 64 * it) + r] = qnorm * fmaf(xp.x, xp.x, xp.y * xp.y);
                     const uint32_t k = k0 + (uint32_t)it * step;
-                    if (m - k < ps_count) Pm[-(ptrdiff_t)((size_t)it * step)] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+                    if (m - k < ps_count) Pm[-(ptrdiff_t)((size_t)it * step)] = qnorm * fmaf(xm.x, xm.x, xm.y * xm.y);
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncthreads();
@@ -742,15 +743,14 @@ __device__ __forceinline__ void pass2_body(const float2 *__restrict__ work, floa
 #pragma unroll
             for (int it = 0; it < ITERS; ++it) {
                 const float2 za = pa[CPOS * it], zb = pb[-CPOS * it];
-                const float2 e = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
-                const float2 d = make_float2(0.5f * (za.x - zb.x), 0.5f * (za.y + zb.y));
-                const float2 o = make_float2(d.y, -d.x);
+                const float2 e = make_float2(za.x + zb.x, za.y - zb.y); // 2E, 2O: the factor 1/4 sits in qnorm (exact)
+                const float2 o = make_float2(za.y + zb.y, zb.x - za.x);
                 const float2 w = cmul(wa, __ldg(twb + KSTEP * it));
                 const float2 wo = cmul(w, o);
                 const float2 xp = cadd(e, wo), xm = csub(e, wo);
                 const uint32_t k = k0 + (uint32_t)it * step;
-                if (k < ps_count) Pk[(size_t)it * step] = norm * fmaf(xp.x, xp.x, xp.y * xp.y);
-                if (m - k < ps_count) Pm[-(ptrdiff_t)((size_t)it * step)] = norm * fmaf(xm.x, xm.x, xm.y * xm.y);
+                if (k < ps_count) Pk[(size_t)it * step] = qnorm * fmaf(xp.x, xp.x, xp.y * xp.y);
+                if (m - k < ps_count) Pm[-(ptrdiff_t)((size_t)it * step)] = qnorm * fmaf(xm.x, xm.x, xm.y * xm.y);
             }
             return;
         }
