@@ -27,9 +27,10 @@
 //   (3) del_t of the inner samples lies between the values at the two ends of the group, up to rounding: the computed
 //       phase fl(fl(Omega*fl(i*dt)) + Psi0) is monotone in i, so is the expansion variable d while the table cell
 //       does not change, and the table polynomial is monotone in d over a group (at the two cells where its
-//       derivative changes sign the excursion is below 1e-10).  What is not monotone is the rounding of the seven
-//       operations behind d: at most 7e-7 * |tau|*step_inv per value.  eta = 2.5e-6*|tau|*step_inv + 1e-6 covers the
-//       three values involved with room to spare.
+//       derivative changes sign the values may leave the interval of the two ends by at most (group phase span)^2 / 8,
+//       which the precondition span < 3e-3 rad keeps below 1.2e-6; physical orbits span 1e-5 rad).  What is not monotone is the rounding of the seven
+//       operations behind d: at most 3.7e-7 * |tau|*step_inv per value.  eta = 4e-6*|tau|*step_inv + 1e-6 is twice the sum
+//       of two such roundings (7.4e-7) and the excursion (1.2e-6), all times |tau|*step_inv.
 // A group falls back to evaluating all of its samples when its ends lie in different table cells, when the two
 // bounds of (1) disagree (a shift change may lie inside), when i - x crosses a binade or is below 1.  A warp owns 512
 // consecutive samples per step; when all 32 groups are proven with the same shift (about 60 % of the steps) the step is a
@@ -137,8 +138,8 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
     const bool packed_ok = (fabsf(tp.Omega) * ((float)nu * g.dt) + fabsf(tp.Psi0)) * BRP_TWO_PI_INV < 4.0e6f;
     // run detection additionally needs a group to span far less than one table cell (1/64 cycle)
     const float amp = fabsf(tp.tau) * g.step_inv;
-    const bool runs_ok = MODE == 2 && packed_ok && fabsf(tp.Omega) * g.dt * (float)kGroupLen < 0.01f && amp < 4.0e6f;
-    const float eta = 2.5e-6f * amp + 1.0e-6f;
+    const bool runs_ok = MODE == 2 && packed_ok && fabsf(tp.Omega) * g.dt * (float)kGroupLen < 3.0e-3f && amp < 4.0e6f;
+    const float eta = 4.0e-6f * amp + 1.0e-6f;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
     // four samples i0..i0+3 by the timing model itself

@@ -86,7 +86,9 @@ ADVERSARIAL = np.array([
     [120.0, 1.0, 1.0],           # amplitude 15 000 samples, 2.3 orbits per work-unit
     [40.0, 3.0, 5.5],            # amplitude 46 000 samples, slope 0.47 samples/sample
     [11.0, 0.8, 0.1],            # 25 orbits: many table-cell and cycle boundaries
-    [2.0, 0.05, 2.0],            # a table cell lasts ~480 samples
+    [2.0, 0.05, 2.0],            # a table cell lasts ~480 samples (just beyond the phase span run detection accepts)
+    [2.3, 0.3, 1.0],             # just inside that span: 2.9e-3 rad per group, amplitude 4 600 samples
+    [3.0, 0.2, 0.5],             # 2.2e-3 rad per group, amplitude 3 000 samples, slope 0.42 samples/sample
     [0.3, 0.01, 4.0],            # a table cell lasts ~70 samples
     [900.0, -0.3, 3.0],          # negative amplitude
     [1500.0, 0.33, -40.0],       # negative phase, several cycles
