@@ -90,7 +90,8 @@ EXPORTED_SYMBOLS = [
     "brp_search_set_series_device", "brp_search_reset", "brp_search_run", "brp_search_sync", "brp_search_collect",
     "brp_search_last_run_ms", "brp_search_stream", "brp_search_kernel_launches", "brp_search_profile_batch",
     "brp_stage_resample", "brp_stage_resample_compare", "brp_stage_spectrum", "brp_stage_spectrum_of", "brp_stage_harmonic_summing",
-    "brp_stage_sin_lut", "brp_stage_round_index", "brp_resample_noalloc", "brp_whiten_series",
+    "brp_stage_sin_lut", "brp_stage_round_index", "brp_resample_noalloc", "brp_whiten_series", "brp_whiten_series_zap",
+    "brp_zaplist_read", "brp_zaplist_free", "brp_zap_noise",
 ]
 
 
@@ -155,6 +156,13 @@ lib.brp_resample_noalloc.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINT
                                      C.c_void_p, C.c_void_p, C.c_void_p]
 
 lib.brp_whiten_series.argtypes = [C.c_int, _f32, C.c_uint32, C.c_float, C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]
+lib.brp_whiten_series_zap.argtypes = [C.c_int, _f32, C.c_uint32, C.c_float, C.c_uint32, C.c_double, C.c_void_p, C.c_uint32,
+                                      C.POINTER(C.c_float)]
+lib.brp_zaplist_read.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.c_uint32)]
+lib.brp_zaplist_free.argtypes = [C.POINTER(C.c_double)]
+lib.brp_zaplist_free.restype = None
+lib.brp_zap_noise.argtypes = [C.c_uint32, C.c_float, C.c_uint32, C.c_double, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32,
+                              C.POINTER(C.c_uint32)]
 
 lib.initialize_cuda.argtypes = [C.c_int, C.POINTER(C.c_int)]
 lib.set_up_resampling.argtypes = [DIfloatPtr, C.POINTER(DIfloatPtr), C.POINTER(ResampParams), C.c_void_p, C.c_void_p]
@@ -401,12 +409,36 @@ def resample_noalloc(d_series: int, g: Geometry, t: Template, d_out: int, d_n_st
                                     d_mean, stream), "brp_resample_noalloc")
 
 
-def whiten_series(series: np.ndarray, padding: float, window: int = 1000, device: int = 0):
-    """``brp_whiten_series``: returns (whitened copy, device milliseconds)."""
+def whiten_series(series: np.ndarray, padding: float, window: int = 1000, device: int = 0, zap: np.ndarray | None = None,
+                  tsample_us: float = 0.0):
+    """``brp_whiten_series_zap``: returns (whitened copy, device milliseconds).  zap = float64[n, 2] (fmin, fmax) in Hz."""
     out = np.ascontiguousarray(series, np.float32).copy()
     ms = C.c_float(0)
-    _check(lib.brp_whiten_series(device, out, out.size, padding, window, 0, C.byref(ms)), "brp_whiten_series")
+    z = np.zeros((0, 2)) if zap is None else np.ascontiguousarray(zap, np.float64).reshape(-1, 2)
+    _check(lib.brp_whiten_series_zap(device, out, out.size, padding, window, tsample_us, z.ctypes.data if len(z) else None, len(z),
+                                     C.byref(ms)), "brp_whiten_series_zap")
     return out, ms.value
+
+
+def read_zaplist(path) -> np.ndarray:
+    """``brp_zaplist_read``: float64[n, 2] (fmin, fmax) in Hz, in file order."""
+    ptr, n = C.POINTER(C.c_double)(), C.c_uint32(0)
+    _check(lib.brp_zaplist_read(str(path).encode(), C.byref(ptr), C.byref(n)), "brp_zaplist_read")
+    try:
+        return np.ctypeslib.as_array(ptr, shape=(max(n.value, 1) * 2,))[: 2 * n.value].reshape(-1, 2).copy()
+    finally:
+        lib.brp_zaplist_free(ptr)
+
+
+def zap_noise(seed_bits: int, padding: float, nsamples: int, tsample_us: float, zap: np.ndarray):
+    """``brp_zap_noise``: (bins uint32[n], values float32[n, 2]) of every draw of the zap step, in draw order (host only)."""
+    z = np.ascontiguousarray(zap, np.float64).reshape(-1, 2)
+    n = C.c_uint32(0)
+    _check(lib.brp_zap_noise(seed_bits, padding, nsamples, tsample_us, z.ctypes.data, len(z), None, None, 0, C.byref(n)), "brp_zap_noise")
+    bins, vals = np.empty(n.value, np.uint32), np.empty((n.value, 2), np.float32)
+    _check(lib.brp_zap_noise(seed_bits, padding, nsamples, tsample_us, z.ctypes.data, len(z), bins.ctypes.data, vals.ctypes.data,
+                             n.value, C.byref(n)), "brp_zap_noise")
+    return bins, vals
 
 
 def search_bank(series: np.ndarray, g: Geometry, bank: np.ndarray, fA: float = 0.08, max_batch: int = 16, device: int = 0):

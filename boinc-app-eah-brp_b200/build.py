@@ -13,8 +13,8 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "libbrp_b200.so"
 CLI = HERE / "brp_b200_search"  # command-line driver over the batched API (csrc/brp_search_main.cpp)
-SOURCES = ["resamp.cu", "fft.cu", "hs.cu", "search.cu", "legacy.cu", "noalloc.cu", "whiten.cu", "host.cpp"]
-HEADERS = ["brp_internal.h", "brp_device.cuh", "../../include/brp_b200.h"]
+SOURCES = ["resamp.cu", "fft.cu", "hs.cu", "search.cu", "legacy.cu", "noalloc.cu", "whiten.cu", "host.cpp", "zap.cpp"]
+HEADERS = ["brp_internal.h", "brp_device.cuh", "ziggurat_tables.h", "../../include/brp_b200.h"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

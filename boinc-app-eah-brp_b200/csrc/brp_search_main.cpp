@@ -38,7 +38,7 @@ void usage(const char *argv0)
            " -o, --output_file      string  candidate file\n"
            " -t, --template_bank    string  template bank (P tau Psi0 per line)\n"
            " -c, --checkpoint_file  string  checkpoint file (read on start if present)\n"
-           " -l, --zaplist_file     string  zap list (only an EMPTY list is supported with -W)\n"
+           " -l, --zaplist_file     string  zap list: \"fmin fmax\" in Hz per line (required with -W)\n"
            " -f, --f0               float   maximum signal frequency in Hz (default 250)\n"
            " -A, --false_alarm      float   false alarm probability (default 0.04)\n"
            " -P, --padding          float   padding factor (default 1.0)\n"
@@ -126,21 +126,6 @@ int parse(int argc, char **argv, Options &o)
     return 0;
 }
 
-/* number of non-comment lines of the zap list; the reference reads "%lg %lg" pairs (demod_binary.c:993-1023) */
-int count_zap_ranges(const char *path, unsigned *n)
-{
-    *n = 0;
-    FILE *f = fopen(path, "r");
-    if (!f) return RADPUL_EFILE;
-    char line[256];
-    while (fgets(line, sizeof line, f)) {
-        double a, b;
-        if (sscanf(line, "%lg %lg", &a, &b) == 2) ++*n;
-    }
-    fclose(f);
-    return 0;
-}
-
 double now_s()
 {
     struct timespec ts;
@@ -203,11 +188,18 @@ int main(int argc, char **argv)
 
     /* ---- whitening, once per work-unit (demod_binary.c:858-1079) ---- */
     if (o.white) {
-        unsigned n_zap = 0;
-        if (o.zaplist) CHECK(count_zap_ranges(o.zaplist, &n_zap));
+        /* the reference opens the zap list unconditionally once -W is given (:982-989) */
+        if (!o.zaplist) {
+            fprintf(stderr, "Couldn't open zaplist file: (none given; -W needs -l)\n");
+            return RADPUL_EFILE;
+        }
+        double *zap = nullptr;
+        uint32_t n_zap = 0;
+        CHECK(brp_zaplist_read(o.zaplist, &zap, &n_zap));
         float ms = 0;
-        CHECK(brp_whiten_series(o.device, series, nu, o.padding, o.window, n_zap, &ms));
-        if (o.debug) fprintf(stderr, "Whitening: %.2f ms on the device\n", ms);
+        CHECK(brp_whiten_series_zap(o.device, series, nu, o.padding, o.window, tsample_us, zap, n_zap, &ms));
+        brp_zaplist_free(zap);
+        if (o.debug) fprintf(stderr, "Whitening: %.2f ms on the device, %u zap ranges\n", ms, n_zap);
     }
 
     /* ---- the template loop, chunk by chunk ---- */
@@ -236,7 +228,7 @@ int main(int argc, char **argv)
     double t_last_cp = t_start;
     uint32_t pos = done;
     long budget = o.max_templates;
-    bool stopped_early = false;
+    bool stopped_early = false, wrote_checkpoint = false;
     while (pos < n_templates) {
         uint32_t n = std::min<uint32_t>(o.chunk, n_templates - pos);
         if (budget >= 0) {
@@ -256,6 +248,7 @@ int main(int argc, char **argv)
             CHECK(snapshot(merged.data()));
             CHECK(brp_checkpoint_write(o.checkpoint, pos, o.input, merged.data()));
             t_last_cp = now_s();
+            wrote_checkpoint = true;
             if (o.debug) fprintf(stderr, "Checkpoint at template %u\n", pos);
         }
     }
@@ -265,7 +258,7 @@ int main(int argc, char **argv)
         fprintf(stderr, "%u templates in %.3f s (%.0f templates/s)\n", pos - done, t_loop, (pos - done) / std::max(t_loop, 1e-9));
 
     if (stopped_early) {
-        fprintf(stderr, "Stopped after %u of %u templates%s.\n", pos, n_templates, o.checkpoint ? "; checkpoint written" : "");
+        fprintf(stderr, "Stopped after %u of %u templates%s.\n", pos, n_templates, wrote_checkpoint ? "; checkpoint written" : "");
         brp_search_destroy(s);
         brp_bank_free(bank);
         return 0;

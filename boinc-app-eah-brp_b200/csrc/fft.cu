@@ -1033,6 +1033,9 @@ static int pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride
     if (p.m1 % kTmaRows != 0 || p.parts < 1) return 0;
     // more than one part: only valid when no sample can sit beyond row 2048 (a row is 2*m1 samples)
     if (p.parts > 1 && (n_steps_bound == 0 || n_steps_bound > 2u * p.m1 * (uint32_t)kTmaL)) return 0;
+    // the kernel fetches whole boxes of kTmaBox rows up to the one that holds sample n_steps - 1: unless the samples a
+    // template can have fill a whole number of boxes, the last box would read past the end of the caller's buffer
+    if ((n_steps_bound ? n_steps_bound : p.n) % ((uint32_t)kTmaBox * 2u * p.m1) != 0) return 0;
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc) return 0;
     static bool configured_on[64]; // function attributes are per device

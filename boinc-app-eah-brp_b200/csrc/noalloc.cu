@@ -27,7 +27,11 @@
 // on one stream, or order them with events.
 //
 // The arithmetic is the library's resampler (resamp.cu / brp_device.cuh; reference semantics
-// demod_binary_resamp_cpu.c:80-136), so results equal those of brp_stage_resample / run_resampling.
+// demod_binary_resamp_cpu.c:80-136): n_steps and the gathered samples equal those of brp_stage_resample /
+// run_resampling bit for bit; the mean is summed in double like theirs but over differently shaped
+// partial sums, so it agrees to the last float ulp or one next to it (tests hold it to 1e-6).
+// The remembered scratch address belongs to the device's current context: after cudaDeviceReset it is
+// stale, and this entry point must not be used again in that process.
 #include <stdio.h>
 
 #include <mutex>

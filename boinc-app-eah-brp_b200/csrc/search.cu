@@ -478,13 +478,14 @@ int brp_stage_resample_compare(brp_search *s, const double *bank, uint32_t n_tem
     return 0;
 }
 
-static int spectrum_common(brp_search *s, const float *d_in, size_t in_stride, float *ps_out, uint32_t count)
+// n_steps_bound: how many samples of d_in can be valid (= how far the FFT's first pass may read)
+static int spectrum_common(brp_search *s, const float *d_in, size_t in_stride, float *ps_out, uint32_t count, uint32_t n_steps_bound)
 {
     if (count > s->g.fft_size) return RADPUL_EVAL;
     if (!s->d_tap_ps) CU_TRY(cudaMalloc((void **)&s->d_tap_ps, sizeof(float) * (s->g.fft_size + 32)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     const float norm = 1.0f / (float)s->g.nsamples;
     CU_TRY(brp_launch_fft_power(s->plan, d_in, in_stride, s->d_nsteps, s->d_mean, s->d_work, s->d_tap_ps, s->g.fft_size + 32, count,
-                                norm, 1, s->stream, NULL),
+                                norm, 1, s->stream, NULL, n_steps_bound),
            RADPUL_CUDA_FFT_EXEC);
     s->launches += 2;
     CU_TRY(cudaMemcpyAsync(ps_out, s->d_tap_ps, sizeof(float) * count, cudaMemcpyDeviceToHost, s->stream), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
@@ -497,7 +498,7 @@ int brp_stage_spectrum(brp_search *s, float *ps_out, uint32_t count)
     if (!s || !ps_out) return RADPUL_EVAL;
     CU_TRY(cudaSetDevice(s->device), RADPUL_CUDA_DEVICE_SET);
     // slot 0 holds the series resampled by the last brp_stage_resample, with its n_steps and mean
-    return spectrum_common(s, s->d_resamp, s->rs_stride, ps_out, count);
+    return spectrum_common(s, s->d_resamp, s->rs_stride, ps_out, count, s->g.nsamples_unpadded);
 }
 
 int brp_stage_spectrum_of(brp_search *s, const float *host_series_n, float *ps_out, uint32_t count)
@@ -512,7 +513,7 @@ int brp_stage_spectrum_of(brp_search *s, const float *host_series_n, float *ps_o
     CU_TRY(cudaMemcpyAsync(s->d_nsteps, &full, sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     CU_TRY(cudaMemcpyAsync(s->d_mean, &zero, sizeof(float), cudaMemcpyHostToDevice, s->stream), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     CU_TRY(cudaStreamSynchronize(s->stream), RADPUL_CUDA_KERNEL_INVOKE);
-    return spectrum_common(s, s->d_tap_series, nfull, ps_out, count);
+    return spectrum_common(s, s->d_tap_series, nfull, ps_out, count, s->g.nsamples);
 }
 
 int brp_stage_harmonic_summing(brp_search *s, const float *host_ps, const float thr[5], uint32_t tmpl_index, brp_hit *hits,

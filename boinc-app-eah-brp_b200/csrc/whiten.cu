@@ -7,16 +7,22 @@
 //   4. scales X_{i+window/2} by sqrt(ln 2 / median_i)                                   (:964-969)
 //   5. replaces zap-list bins by Gaussian noise (GSL taus2 + ziggurat)                  (:982-1033)
 //   6. zeroes window/2 bins at either end, transforms back, multiplies by 1/sqrt(N)     (:1038-1069)
-// Steps 1-4 and 6 are done here with the library's own FFT kernels (fft.cu) and an exact sliding median;
-// step 5 needs GSL's ziggurat tables for bit parity, which are not in the reference tree, so a non-empty
-// zap list is not supported (the caller gets RADPUL_EVAL and can fall back to an unzapped search).
+// Steps 1-4 and 6 are done here with the library's own FFT kernels (fft.cu) and an exact sliding median.  The noise of
+// step 5 comes from a strictly sequential generator and is only a few thousand numbers: it is drawn on the host in the
+// reference's order (zap.cpp) and scattered into the spectrum by zap_kernel between steps 4 and 6.
 //
 // The median is exact (same order statistics as rngmed.c, even windows average the two middle values in
 // double like rngmed.c:179,329): see running_median_kernel.
 #include <math.h>
 #include <stdio.h>
 
+#include <vector>
+
 #include "brp_internal.h"
+
+// zap.cpp: the replaced bins and their noise values, drawn in the reference's order
+int brp_zap_draw(uint32_t seed_bits, float padding, uint32_t nsamples, double tsample_us, const double *zap, uint32_t n_zap,
+                 uint32_t fft_size, std::vector<uint32_t> &bins, std::vector<float2> &values);
 
 namespace {
 
@@ -127,6 +133,18 @@ __global__ void scale_and_edge_kernel(float2 *__restrict__ X, const float *__res
     X[k] = v;
 }
 
+// step 5: X[bin] = noise for the bins of the zap list (:1018-1019); bins inside the zeroed edges stay zero (:1038-1044 come
+// later in the reference and win)
+__global__ void zap_kernel(float2 *__restrict__ X, const uint32_t *__restrict__ bins, const float2 *__restrict__ values, uint32_t n,
+                           uint32_t f, uint32_t window_2)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = bins[i];
+    if (k < window_2 || k + window_2 >= f) return;
+    X[k] = values[i];
+}
+
 // backward real transform of X[0..M] as one complex transform of length M:
 //   Z'[k] = (X[k] + conj X[M-k]) + i W_N^{-k} (X[k] - conj X[M-k]),   x = conj(FFT(conj Z')) interleaved
 __global__ void inverse_prep_kernel(const float2 *__restrict__ X, float2 *__restrict__ zc, uint32_t m, float two_over_n)
@@ -154,15 +172,11 @@ __global__ void inverse_prep_kernel(const float2 *__restrict__ X, float2 *__rest
         }                                                                                                    \
     } while (0)
 
-extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
-                                 uint32_t n_zap_ranges, float *device_ms)
+extern "C" int brp_whiten_series_zap(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
+                                     double tsample_us, const double *zap_ranges, uint32_t n_zap_ranges, float *device_ms)
 {
     if (!series || nsamples_unpadded < 2 || padding < 1.0f || padding > 10.0f) return RADPUL_EVAL;
-    if (n_zap_ranges != 0) {
-        fprintf(stderr, "[brp_b200] brp_whiten_series: zap-list noise replacement is not supported "
-                        "(it needs GSL's ziggurat tables for parity with demod_binary.c:1012-1021)\n");
-        return RADPUL_EVAL;
-    }
+    if (n_zap_ranges != 0 && (!zap_ranges || !(tsample_us > 0.0))) return RADPUL_EVAL;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) return RADPUL_CUDA_DEVICE_FIND;
     if (cudaSetDevice(device) != cudaSuccess) return RADPUL_CUDA_DEVICE_SET;
@@ -179,11 +193,19 @@ extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_un
     int rc = 0;
     BrpFftPlan plan;
     float *d_x = NULL, *d_ps = NULL, *d_med = NULL, *d_out = NULL, *d_mean = NULL;
-    float2 *d_X = NULL, *d_zc = NULL, *d_work = NULL;
-    uint32_t *d_ns = NULL;
+    float2 *d_X = NULL, *d_zc = NULL, *d_work = NULL, *d_zap_val = NULL;
+    uint32_t *d_ns = NULL, *d_zap_bin = NULL;
+    std::vector<uint32_t> zap_bins;
+    std::vector<float2> zap_vals;
     cudaEvent_t ev0 = NULL, ev1 = NULL;
     cudaStream_t st = 0;
     memset(&plan, 0, sizeof(plan));
+    {
+        uint32_t seed_bits; // the first sample's bit pattern, before anything is changed (:917)
+        memcpy(&seed_bits, series, sizeof(seed_bits));
+        rc = brp_zap_draw(seed_bits, padding, n, tsample_us, zap_ranges, n_zap_ranges, f, zap_bins, zap_vals);
+        if (rc) return rc;
+    }
     rc = brp_fft_plan_create(&plan, n);
     if (rc) return rc;
     {
@@ -205,6 +227,12 @@ extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_un
         WH_TRY(cudaMemcpy(d_x, series, sizeof(float) * nu, cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
         WH_TRY(cudaMemcpy(d_ns, ns_host, sizeof(ns_host), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
         WH_TRY(cudaMemcpy(d_mean, &zero, sizeof(float), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+        if (!zap_bins.empty()) {
+            WH_TRY(cudaMalloc((void **)&d_zap_bin, sizeof(uint32_t) * zap_bins.size()), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+            WH_TRY(cudaMalloc((void **)&d_zap_val, sizeof(float2) * zap_vals.size()), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+            WH_TRY(cudaMemcpy(d_zap_bin, zap_bins.data(), sizeof(uint32_t) * zap_bins.size(), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+            WH_TRY(cudaMemcpy(d_zap_val, zap_vals.data(), sizeof(float2) * zap_vals.size(), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+        }
         if (med_smem > 48 * 1024)
             WH_TRY(cudaFuncSetAttribute((const void *)running_median_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, med_smem),
                    RADPUL_CUDA_KERNEL_INVOKE);
@@ -215,6 +243,9 @@ extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_un
         periodogram_kernel<<<(f + 255) / 256, 256, 0, st>>>(d_X, d_ps, f);
         running_median_kernel<<<(white_size + kMedThreads * kMedRun - 1) / (kMedThreads * kMedRun), kMedThreads, med_smem, st>>>(d_ps, f, window, d_med, white_size);
         scale_and_edge_kernel<<<(f + 255) / 256, 256, 0, st>>>(d_X, d_med, f, window_2, white_size);
+        // 5. zap-list noise
+        if (!zap_bins.empty())
+            zap_kernel<<<((uint32_t)zap_bins.size() + 255) / 256, 256, 0, st>>>(d_X, d_zap_bin, d_zap_val, (uint32_t)zap_bins.size(), f, window_2);
         // 6. backward transform and renormalisation: 1/sqrt((float)N) held in a float (:1066)
         inverse_prep_kernel<<<(m + 255) / 256, 256, 0, st>>>(d_X, d_zc, m, 2.0f / (float)n);
         WH_TRY(cudaGetLastError(), RADPUL_CUDA_KERNEL_INVOKE);
@@ -226,9 +257,20 @@ extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_un
     }
 done:
     cudaFree(d_x); cudaFree(d_X); cudaFree(d_zc); cudaFree(d_work); cudaFree(d_ps); cudaFree(d_med); cudaFree(d_out);
-    cudaFree(d_ns); cudaFree(d_mean);
+    cudaFree(d_ns); cudaFree(d_mean); cudaFree(d_zap_bin); cudaFree(d_zap_val);
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     brp_fft_plan_destroy(&plan);
     return rc;
+}
+
+// the original entry point: whitening without a zap list
+extern "C" int brp_whiten_series(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
+                                 uint32_t n_zap_ranges, float *device_ms)
+{
+    if (n_zap_ranges != 0) {
+        fprintf(stderr, "[brp_b200] brp_whiten_series: pass the zap ranges to brp_whiten_series_zap\n");
+        return RADPUL_EVAL;
+    }
+    return brp_whiten_series_zap(device, series, nsamples_unpadded, padding, window, 0.0, NULL, 0, device_ms);
 }

@@ -201,7 +201,10 @@ typedef struct brp_search brp_search;
  * templates in flight, FFT tables, the per-bin toplist table (5 x Fu x 8 bytes, zeroed). */
 int brp_search_create(brp_search **out, int device, const brp_geometry *g, float fA, uint32_t max_batch);
 int brp_search_destroy(brp_search *s);
-/* dedispersed (whitened) time series: Nu floats from HOST memory (one H2D copy, cuda/app/demod_binary_cuda.cu:333) */
+/* dedispersed (whitened) time series: Nu floats from HOST memory (one H2D copy, cuda/app/demod_binary_cuda.cu:333).
+ * The copy is enqueued, not awaited: host_series must stay valid and unchanged until brp_search_sync() or
+ * brp_search_collect() has returned (with pageable memory the runtime has staged it by the time this call returns;
+ * with pinned memory it has not). */
 int brp_search_set_series(brp_search *s, const float *host_series);
 /* same from DEVICE memory already resident on `device` (device-to-device copy) */
 int brp_search_set_series_device(brp_search *s, const void *device_series);
@@ -250,11 +253,26 @@ int brp_stage_round_index(int device, const float *f, int32_t *idx_out, uint32_t
 
 /* Whitening pre-step of a work-unit (demod_binary.c:858-1079, once per work-unit, before the template loop): FFT of the
  * zero-padded series, periodogram, exact running median over `window` bins (rngmed.c:48), rescaling to a white spectrum,
- * zeroing of window/2 edge bins, back-transform, 1/sqrt(N).  `series` (HOST, nsamples_unpadded floats) is whitened in
- * place.  The zap-list noise replacement (:982-1033) needs GSL's ziggurat generator and is not supported: n_zap_ranges
- * must be 0 (RADPUL_EVAL otherwise).  device_ms (optional) receives the device time of the whole step. */
+ * replacement of the zap-list bins by Gaussian noise (:982-1033), zeroing of window/2 edge bins, back-transform,
+ * 1/sqrt(N).  `series` (HOST, nsamples_unpadded floats) is whitened in place.  zap_ranges: n_zap_ranges (fmin, fmax)
+ * pairs in Hz in file order (brp_zaplist_read), may be NULL when n_zap_ranges == 0; tsample_us (header.tsample) is only
+ * used to turn them into bin numbers (:996,1012-1013).  The noise is drawn on the host in the reference's order from
+ * restatements of GSL's taus2 and ziggurat Gaussian (GSL is not part of the reference tree: parity with libgsl
+ * unpinned).  device_ms (optional) receives the device time of the whole step. */
+int brp_whiten_series_zap(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
+                          double tsample_us, const double *zap_ranges, uint32_t n_zap_ranges, float *device_ms);
+/* the same without a zap list (n_zap_ranges must be 0, RADPUL_EVAL otherwise) */
 int brp_whiten_series(int device, float *series, uint32_t nsamples_unpadded, float padding, uint32_t window,
                       uint32_t n_zap_ranges, float *device_ms);
+/* zap list file, one "%lg %lg" pair (fmin fmax, Hz) per line (demod_binary.c:982-1009): RADPUL_EFILE if it cannot be
+ * opened, RADPUL_EIO on a line that does not parse.  Allocates *ranges (2 doubles per range; brp_zaplist_free). */
+int brp_zaplist_read(const char *path, double **ranges, uint32_t *n_ranges);
+void brp_zaplist_free(double *ranges);
+/* the noise draws of the zap step alone (no GPU), in draw order: bins_out[i] and out[2i], out[2i+1] = bin, re, im of
+ * draw i for i < max_bins (either may be NULL); *n_bins_out = total number of bins drawn.  seed_bits = bit pattern of
+ * the first sample of the un-whitened series (:917), nsamples = PADDED length. */
+int brp_zap_noise(uint32_t seed_bits, float padding, uint32_t nsamples, double tsample_us, const double *zap_ranges,
+                  uint32_t n_zap_ranges, uint32_t *bins_out, float *out, uint32_t max_bins, uint32_t *n_bins_out);
 
 /* =====================================================================================
  * 4. Resampling without any device allocation
@@ -274,7 +292,7 @@ int brp_whiten_series(int device, float *series, uint32_t nsamples_unpadded, flo
  * The kernel's scratch is a fixed array of BRP_NOALLOC_SCRATCH_BYTES inside the library image, held by every
  * GPU that loads the library until the process exits; series longer than BRP_NOALLOC_MAX_SAMPLES are
  * rejected with RADPUL_EVAL and a message.  The first call on a GPU looks the array's address up once; issue
- * that first call before beginning any stream capture.  All calls on a GPU share the array: calls that may
+ * that first call before beginning any stream capture (the address dies with cudaDeviceReset: do not call again after one).  All calls on a GPU share the array: calls that may
  * overlap on the device (different streams or threads) race and must be ordered by the caller. */
 #define BRP_NOALLOC_MAX_SAMPLES (1u << 24)
 #define BRP_NOALLOC_SCRATCH_BYTES (8u * (BRP_NOALLOC_MAX_SAMPLES / 4096u) + 256u)

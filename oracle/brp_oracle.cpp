@@ -7,6 +7,7 @@
  */
 #include "brp_oracle.h"
 #include "fft_double.h"
+#include "../boinc-app-eah-brp_b200/csrc/ziggurat_tables.h" /* data only: regenerated GSL ziggurat tables */
 
 #include <math.h>
 #include <stdio.h>
@@ -455,8 +456,54 @@ int brp_oracle_rngmed(const float *input, uint32_t length, uint32_t bsize, float
     return 0;
 }
 
-/* demod_binary.c:858-1079 with an empty zap list */
-int brp_oracle_whiten(float *series, uint32_t n_unpadded, float padding, uint32_t window)
+/* ---- zap-list noise: GSL taus2 + gsl_ran_gaussian_ziggurat restated (GSL is not under /root/reference: the generator
+ * follows its published description, the tables are regenerated by tools/gen_ziggurat.py -> parity with libgsl unpinned;
+ * pinned against oracle/_ref, whose GSL stand-in is oracle/shim_gsl.c) ---- */
+struct Taus2 { unsigned long s1, s2, s3; };
+static unsigned long taus2_get(Taus2 *r)
+{
+#define BRP_TAUS(s, a, b, c, d) ((((s) & (c)) << (d)) & 0xffffffffUL) ^ (((((s) << (a)) & 0xffffffffUL) ^ (s)) >> (b))
+    r->s1 = BRP_TAUS(r->s1, 13, 19, 4294967294UL, 12);
+    r->s2 = BRP_TAUS(r->s2, 2, 25, 4294967288UL, 4);
+    r->s3 = BRP_TAUS(r->s3, 3, 11, 4294967280UL, 17);
+#undef BRP_TAUS
+    return r->s1 ^ r->s2 ^ r->s3;
+}
+static void taus2_set(Taus2 *r, unsigned long s)
+{
+    if (s == 0) s = 1;
+    r->s1 = (69069UL * s) & 0xffffffffUL;  if (r->s1 < 2) r->s1 += 2UL;
+    r->s2 = (69069UL * r->s1) & 0xffffffffUL; if (r->s2 < 8) r->s2 += 8UL;
+    r->s3 = (69069UL * r->s2) & 0xffffffffUL; if (r->s3 < 16) r->s3 += 16UL;
+    for (int i = 0; i < 6; i++) taus2_get(r);
+}
+static double zig_gaussian(Taus2 *r, double sigma)
+{
+    for (;;) {
+        const unsigned long k = taus2_get(r);
+        unsigned long i = k & 0xFF;
+        const unsigned long j = (k >> 8) & 0xFFFFFF;
+        const int sign = (i & 0x80) ? +1 : -1;
+        i &= 0x7f;
+        double x = j * brp_zig_wtab[i], y;
+        if (j < brp_zig_ktab[i]) return sign * sigma * x;
+        if (i < 127) {
+            const double y0 = brp_zig_ytab[i], y1 = brp_zig_ytab[i + 1];
+            y = y1 + (y0 - y1) * (taus2_get(r) / 4294967296.0);
+        } else {
+            const double U1 = 1.0 - taus2_get(r) / 4294967296.0;
+            const double U2 = taus2_get(r) / 4294967296.0;
+            x = BRP_ZIG_R - log(U1) / BRP_ZIG_R;
+            y = exp(-BRP_ZIG_R * (x - 0.5 * BRP_ZIG_R)) * U2;
+        }
+        if (y < exp(-0.5 * x * x)) return sign * sigma * x;
+    }
+}
+
+/* demod_binary.c:858-1079.  zap: n_zap pairs (fmin, fmax) in Hz in file order (:993-1023), may be NULL with n_zap = 0;
+ * tsample_us is only used for the bin numbers of the zap ranges (:996,1012-1013). */
+int brp_oracle_whiten_zap(float *series, uint32_t n_unpadded, float padding, uint32_t window, double tsample_us,
+                          const double *zap, uint32_t n_zap)
 {
     uint32_t nsamples = n_unpadded;
     nsamples = (int)(padding * nsamples + 0.5);
@@ -472,6 +519,8 @@ int brp_oracle_whiten(float *series, uint32_t n_unpadded, float padding, uint32_
     float *med = (float *)calloc(white_size, sizeof(float));
     if (!time_series || !fft || !ps || !med) return 1;
     for (uint32_t i = 0; i < n_unpadded; i++) time_series[i] = series[i];
+    int32_t seed;
+    memcpy(&seed, series, sizeof(seed)); /* :917 the first sample's bit pattern */
     drfft_execute_f32(plan, time_series, fft);
     for (unsigned int i = 1; i < fft_size; i++) {
         const double re = fft[2 * i], im = fft[2 * i + 1];
@@ -483,6 +532,20 @@ int brp_oracle_whiten(float *series, uint32_t n_unpadded, float padding, uint32_
         fft[2 * (i + window_2)] *= factor;
         fft[2 * (i + window_2) + 1] *= factor;
     }
+    if (n_zap) { /* :990-1023 */
+        Taus2 r;
+        taus2_set(&r, (unsigned long)seed);
+        const double t_obs = nsamples * tsample_us * 1.0e-6;
+        const double sigma = M_SQRT1_2 * sqrt(padding);
+        for (uint32_t z = 0; z < n_zap; z++) {
+            const unsigned int idx_min = (unsigned int)(zap[2 * z] * t_obs + 0.5);
+            const unsigned int idx_max = (unsigned int)(zap[2 * z + 1] * t_obs + 0.5);
+            for (unsigned int idx = idx_min; idx <= idx_max; idx++) {
+                const float re = zig_gaussian(&r, sigma), im = zig_gaussian(&r, sigma);
+                if (idx < fft_size) { fft[2 * idx] = re; fft[2 * idx + 1] = im; } /* the reference writes out of bounds beyond */
+            }
+        }
+    }
     for (unsigned int i = 0; i < window_2; i++) {
         fft[2 * i] = fft[2 * i + 1] = 0.0f;
         fft[2 * (fft_size - i - 1)] = fft[2 * (fft_size - i - 1) + 1] = 0.0f;
@@ -493,6 +556,11 @@ int brp_oracle_whiten(float *series, uint32_t n_unpadded, float padding, uint32_
     free(time_series); free(fft); free(ps); free(med);
     drfft_plan_destroy(plan);
     return 0;
+}
+
+int brp_oracle_whiten(float *series, uint32_t n_unpadded, float padding, uint32_t window)
+{
+    return brp_oracle_whiten_zap(series, n_unpadded, padding, window, 0.0, NULL, 0);
 }
 
 } /* extern "C" */

@@ -86,10 +86,13 @@ int brp_oracle_format_candidates(brp_oracle_cand *cands, const brp_oracle_geomet
 int brp_oracle_search(const float *series, const brp_oracle_geometry *g, float fA, const double *bank,
                       uint32_t n_templates, brp_oracle_cand *cands_out, int32_t *tmpl_idx_out);
 
-/* whitening pre-step WITHOUT zap-list noise, demod_binary.c:858-1079 (rngmed.c:48 restated as an exact sliding median):
- * series (nsamples_unpadded floats) is replaced by its whitened version.  The zap-list replacement (:982-1033) needs
- * GSL's ziggurat tables and is not restated. */
+/* whitening pre-step with an empty zap list, demod_binary.c:858-1079 (rngmed.c:48 restated as an exact sliding median):
+ * series (nsamples_unpadded floats) is replaced by its whitened version. */
 int brp_oracle_whiten(float *series, uint32_t nsamples_unpadded, float padding, uint32_t window);
+/* the same with the zap-list noise replacement: n_zap (fmin, fmax) pairs in Hz, in file order.  GSL's taus2 and ziggurat
+ * Gaussian are restated from their published descriptions (tables: tools/gen_ziggurat.py) -> parity with libgsl unpinned */
+int brp_oracle_whiten_zap(float *series, uint32_t nsamples_unpadded, float padding, uint32_t window, double tsample_us,
+                          const double *zap, uint32_t n_zap);
 /* exact running median, semantics of rngmed.c: medians[i] = median(input[i .. i+bsize-1]); even bsize: (a+b)/2.0 */
 int brp_oracle_rngmed(const float *input, uint32_t length, uint32_t bsize, float *medians);
 

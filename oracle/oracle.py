@@ -82,6 +82,7 @@ class Oracle:
         L.brp_oracle_finalize.argtypes = [C.c_void_p, C.c_void_p]
         L.brp_oracle_format_candidates.argtypes = [C.c_void_p, C.POINTER(Geometry), C.c_double, C.c_char_p, C.c_int]
         L.brp_oracle_whiten.argtypes = [f32p, C.c_uint32, C.c_float, C.c_uint32]
+        L.brp_oracle_whiten_zap.argtypes = [f32p, C.c_uint32, C.c_float, C.c_uint32, C.c_double, C.c_void_p, C.c_uint32]
         L.brp_oracle_rngmed.argtypes = [f32p, C.c_uint32, C.c_uint32, f32p]
         L.brp_oracle_search.argtypes = [f32p, C.POINTER(Geometry), C.c_float, f64p, C.c_uint32, C.c_void_p, C.c_void_p]
 
@@ -134,6 +135,14 @@ class Oracle:
     def whiten(self, series: np.ndarray, padding: float, window: int) -> np.ndarray:
         out = np.ascontiguousarray(series, np.float32).copy()
         rc = self.L.brp_oracle_whiten(out, out.size, padding, window)
+        assert rc == 0
+        return out
+
+    def whiten_zap(self, series: np.ndarray, padding: float, window: int, tsample_us: float, zap: np.ndarray) -> np.ndarray:
+        """whitening with zap-list noise; zap = float64[n, 2] (fmin, fmax) in Hz in file order"""
+        out = np.ascontiguousarray(series, np.float32).copy()
+        zap = np.ascontiguousarray(zap, np.float64).reshape(-1, 2)
+        rc = self.L.brp_oracle_whiten_zap(out, out.size, padding, window, tsample_us, zap.ctypes.data if len(zap) else None, len(zap))
         assert rc == 0
         return out
 

@@ -79,15 +79,30 @@ def test_cli_with_whitening(wu, golden):
     assert len({key(l) for l in got[:-1]} & {key(l) for l in ref[:-1]}) >= 0.9 * (len(ref) - 1)
 
 
+@pytest.mark.parametrize("tag,padding", [("CZ1", "1.0"), ("CZ3", "3.0")])
+def test_cli_with_whitening_and_zap_list(wu, tag, padding):
+    """-W -l <non-empty zap list>: the reference's production form of the command (bench_single.sh:28)."""
+    gz = np.load(Path(__file__).resolve().parent / "golden" / "golden_zap.npz", allow_pickle=False)
+    (wu / "zap.txt").write_bytes(bytes(gz["zap_text"]))
+    run_cli(wu, "-W", "-l", str(wu / "zap.txt"), padding=padding)
+    got = (wu / "out.cand").read_text().splitlines()
+    ref = bytes(gz[f"{tag}_candfile"]).decode().splitlines()
+    key = lambda line: tuple(line.split()[:4] + [line.split()[6]])
+    assert got[-1] == "%DONE%" and [key(l) for l in got[:10]] == [key(l) for l in ref[:10]]
+    assert len({key(l) for l in got[:-1]} & {key(l) for l in ref[:-1]}) >= 0.9 * (len(ref) - 1)
+
+
 def test_cli_error_paths(wu):
     run_cli(wu, "--max_templates", "2", "--checkpoint_period", "0")
     (wu / "other.binary").write_bytes((wu / "wu.binary").read_bytes())
     cmd = [str(EXE), "-i", str(wu / "other.binary"), "-o", str(wu / "o"), "-t", str(wu / "bank.txt"), "-c", str(wu / "cp.cpt")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
     assert r.returncode == brp_b200.RADPUL_EVAL and "doesn't agree" in r.stderr       # demod_binary.c:589-593
-    (wu / "zap.txt").write_text("60.0 0.1\n120.0 0.1\n")
-    r = run_cli(wu, "-W", "-l", str(wu / "zap.txt"), cpt=None, check=False)            # zap-list noise is not supported
-    assert r.returncode == brp_b200.RADPUL_EVAL
+    r = run_cli(wu, "-W", cpt=None, check=False)                                        # -W opens the zap list unconditionally
+    assert r.returncode == brp_b200.RADPUL_EFILE and "zaplist" in r.stderr              # demod_binary.c:982-989
+    (wu / "zap.txt").write_text("60.0\n")
+    r = run_cli(wu, "-W", "-l", str(wu / "zap.txt"), cpt=None, check=False)            # incomplete line, :1003-1007
+    assert r.returncode == brp_b200.RADPUL_EIO
     r = subprocess.run([str(EXE), "-i", "x.dat", "-o", "o", "-t", "t"], capture_output=True, text=True)
     assert r.returncode == brp_b200.RADPUL_EFILE
     r = subprocess.run([str(EXE), "-P", "0.5"], capture_output=True, text=True)

@@ -80,6 +80,28 @@ def test_resample_unaligned_length_and_dc_offset(oracle):
     s.close()
 
 
+@pytest.mark.parametrize("nu", [(1 << 22) + 4096, 1 << 23])
+def test_resample_long_series_uses_the_literal_double_index_arithmetic(oracle, nu):
+    """Series longer than 2^22 samples: i - del_t can reach 2^23, where the FP32 rounding shortcut is no longer exact, so the
+    resampler switches to the reference's literal (int)((double)f + 0.5) (resample_kernel<0>, demod_binary_resamp_cpu.c:116).
+    Indices, n_steps and gathered samples bit-exact against the oracle."""
+    series, _ = synth.make_series(nu, seed=23, pulsar=None)
+    go = oracle.geometry(nu, synth.TSAMPLE_US, 1.0, 400.0, 1000)
+    g = brp_b200.derive_geometry(1 << 23, synth.TSAMPLE_US, 1.0, 400.0, 1000)     # FFT lengths must be 2^a or 3*2^a
+    g.nsamples_unpadded = nu
+    s = brp_b200.Search(g, max_batch=1)
+    s.set_series(series)
+    for row in ([1462.994097917309, 0.192481315985, 1.753485476554], [660.0, 0.335, 6.2], [1000.0, 0.0, 0.0], [40.0, 3.0, 5.5]):
+        t = brp_b200.derive_template(*row, g.step_inv)
+        res, idx, ns, _ = oracle.resample(series, go, oracle.template(*row, go.step_inv))
+        out, gidx, gns, mean = s.stage_resample(t)
+        assert gns == ns and np.array_equal(gidx[:ns], idx[:ns]), row
+        assert np.array_equal(bits(out[:ns]), bits(res[:ns]))
+        exact = float(np.mean(series[idx[:ns]].astype(np.float64)))
+        assert abs(mean - exact) <= 2e-7 * max(1.0, abs(exact))
+    s.close()
+
+
 ADVERSARIAL = np.array([
     [1000.0, 0.0, 0.0],          # null template: del_t == 0 everywhere
     [660.0, 0.335, 6.2],         # corner of the production bank

@@ -1,7 +1,8 @@
 """brp_resample_noalloc: the resampler for callers that cannot allocate device memory (fixed memory budget, own arena,
 or no tolerance for cudaMalloc's device-wide synchronisation).  Its scratch is a fixed array inside the library, so this
 test checks through the C ABI that it gives what the allocating entry point (brp_stage_resample) gives -- on two calls
-in a row, because the second call finds the first call's leftovers in the shared scratch array.
+in a row, because the second call finds the first call's leftovers in the shared scratch array -- and, directly, what the
+CPU oracle gives (indices are not an output of this entry point, so the gathered samples are compared bit for bit).
 
 Collected last on purpose (file name): a run that stops at the first failure has then already run every other test.
 It passes alone in a fresh process and after the other tests."""
@@ -14,12 +15,14 @@ from brp_b200 import synth
 pytestmark = pytest.mark.gpu
 
 
-def test_noalloc_resampler_matches_allocating_entry_point_twice():
+@pytest.mark.parametrize("log2nu,padding", [(18, 3.0), (23, 1.0)])        # 2^23: beyond 2^22 samples the kernel indexes in double
+def test_noalloc_resampler_matches_allocating_entry_point_twice(oracle, log2nu, padding):
     import torch
 
-    nu = 1 << 18
-    series, _ = synth.make_series(nu, seed=2718)
-    g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, 3.0, 400.0, 1000)      # padded: exercises the mean fill too
+    nu = 1 << log2nu
+    series, _ = synth.make_series(nu, seed=2718, pulsar=None)
+    g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, padding, 400.0, 1000)   # padded: exercises the mean fill too
+    go = oracle.geometry(nu, synth.TSAMPLE_US, padding, 400.0, 1000)
     ref = brp_b200.Search(g, max_batch=1)
     ref.set_series(series)
 
@@ -43,6 +46,11 @@ def test_noalloc_resampler_matches_allocating_entry_point_twice():
         assert np.array_equal(got[:got_ns].view(np.uint32), want[:want_ns].view(np.uint32))   # gathered samples: bit-exact
         assert abs(got_mean - want_mean) <= 1e-6 * max(1.0, abs(want_mean))             # mean: the tolerance of test_gpu_resample.py
         assert np.all(got[got_ns:] == np.float32(got_mean))                             # padding [n_steps, N)
+        # and against the CPU oracle directly (demod_binary_resamp_cpu.c:91-133 restated)
+        res, idx, ns, _ = oracle.resample(series, go, oracle.template(*row, go.step_inv))
+        assert got_ns == ns and np.array_equal(got[:ns].view(np.uint32), res[:ns].view(np.uint32))
+        exact = float(np.mean(series[idx[:ns]].astype(np.float64)))
+        assert abs(got_mean - exact) <= 2e-7 * max(1.0, abs(exact))
     ref.close()
 
 
