@@ -6,6 +6,13 @@
 // one run_resampling/run_fft/run_harmonic_summing round trip per template.  (The unmodified reference driver linked
 // against the eleven legacy symbols is the other way to run this library; see INTEGRATION.md.)
 //
+// Several GPUs of one box (--devices 0-7): one handle per device in this one process, every round of the loop hands each
+// device a contiguous piece of the next stretch of the bank (so the searched templates are always a prefix of the bank and
+// checkpoints keep their meaning), all devices run concurrently, and the per-device hit lists (a few KB each) come back
+// by plain device-to-host copies and are merged on the host by brp_toplist_from_hits -- concatenation is exact, global
+// template indices make "earliest template" well defined.  No NCCL here: inside one process there is nothing to
+// exchange between the devices themselves.
+//
 // There is no CPU path in here: every stage of the search runs in the CUDA kernels of the library, and the program
 // fails with the library's RADPUL_* code when no device is usable.
 #include <stdio.h>
@@ -29,7 +36,31 @@ struct Options {
     double checkpoint_period_s = 60;  /* wall-clock seconds between checkpoints (0 = after every chunk) */
     long max_templates = -1;          /* stop (with a checkpoint) after this many templates of this invocation */
     unsigned batch = 64;              /* templates per kernel launch */
+    std::vector<int> devices;         /* --devices: several GPUs of this box (empty = the one of -D) */
 };
+
+/* "0-3", "0,2,5", "0-1,4": device ordinals in the order given (an ordinal may repeat: several handles on one GPU) */
+bool parse_devices(const char *v, std::vector<int> &out)
+{
+    out.clear();
+    const char *p = v;
+    while (*p) {
+        char *end = nullptr;
+        long a = strtol(p, &end, 10);
+        if (end == p || a < 0) return false;
+        long b = a;
+        if (*end == '-') {
+            p = end + 1;
+            b = strtol(p, &end, 10);
+            if (end == p || b < a) return false;
+        }
+        for (long d = a; d <= b; d++) out.push_back((int)d);
+        if (*end == ',') end++;
+        else if (*end) return false;
+        p = end;
+    }
+    return !out.empty() && out.size() <= 64;
+}
 
 void usage(const char *argv0)
 {
@@ -45,6 +76,7 @@ void usage(const char *argv0)
            " -W, --whitening                whiten the series first\n"
            " -B, --box              int     running-median window (default 1000)\n"
            " -D, --device           int     CUDA device (default 0)\n"
+           "     --devices          list    several GPUs of this box, e.g. 0-7 or 0,2,4: the bank is split over them\n"
            " -z, --debug                    more output\n"
            "     --chunk            int     templates per enqueue between checkpoint opportunities (default 2048)\n"
            "     --batch            int     templates per kernel launch (default 64)\n"
@@ -108,6 +140,11 @@ int parse(int argc, char **argv, Options &o)
                 return RADPUL_EVAL;
             }
             o.device = atoi(v);
+        } else if (strcmp(a, "--devices") == 0) {
+            if (!parse_devices(v, o.devices)) {
+                fprintf(stderr, "Nonsense value: device list %s.\n", v);
+                return RADPUL_EVAL;
+            }
         } else if (strcmp(a, "--chunk") == 0) o.chunk = std::max(1, atoi(v));
         else if (strcmp(a, "--batch") == 0) o.batch = std::max(1, atoi(v));
         else if (strcmp(a, "--checkpoint_period") == 0) o.checkpoint_period_s = atof(v);
@@ -202,20 +239,31 @@ int main(int argc, char **argv)
         if (o.debug) fprintf(stderr, "Whitening: %.2f ms on the device, %u zap ranges\n", ms, n_zap);
     }
 
-    /* ---- the template loop, chunk by chunk ---- */
-    brp_search *s = nullptr;
-    CHECK(brp_search_create(&s, o.device, &g, o.fA, o.batch));
-    CHECK(brp_search_set_series(s, series));
+    /* ---- the template loop, chunk by chunk; one handle per device ---- */
+    if (o.devices.empty()) o.devices.push_back(o.device);
+    const size_t ndev = o.devices.size();
+    std::vector<brp_search *> handles(ndev, nullptr);
+    for (size_t d = 0; d < ndev; d++) {
+        CHECK(brp_search_create(&handles[d], o.devices[d], &g, o.fA, o.batch));
+        CHECK(brp_search_set_series(handles[d], series));
+    }
+    for (size_t d = 0; d < ndev; d++) CHECK(brp_search_sync(handles[d])); /* the copies read `series` */
     brp_series_free(series);
 
-    std::vector<brp_hit> hits(5u * g.fundamental_idx_hi + 1);
+    const size_t cap = 5u * (size_t)g.fundamental_idx_hi + 1;
+    std::vector<brp_hit> hits(cap * ndev);
     std::vector<brp_cand> fresh(BRP_N_CAND), merged(BRP_N_CAND);
-    /* candidates of everything searched so far: checkpoint content merged with this invocation's device table */
+    /* candidates of everything searched so far: checkpoint content merged with this invocation's device tables
+     * (hit lists of the devices concatenated: exact, see brp_toplist_from_hits) */
     auto snapshot = [&](brp_cand *out) -> int {
         uint32_t n_hits = 0;
-        int r = brp_search_collect(s, hits.data(), (uint32_t)hits.size(), &n_hits);
-        if (r) return r;
-        r = brp_toplist_from_hits(hits.data(), n_hits, bank, n_templates, fresh.data(), nullptr);
+        for (size_t d = 0; d < ndev; d++) {
+            uint32_t n_d = 0;
+            int r = brp_search_collect(handles[d], hits.data() + n_hits, (uint32_t)cap, &n_d);
+            if (r) return r;
+            n_hits += n_d;
+        }
+        int r = brp_toplist_from_hits(hits.data(), n_hits, bank, n_templates, fresh.data(), nullptr);
         if (r) return r;
         if (!resumed) {
             memcpy(out, fresh.data(), sizeof(brp_cand) * BRP_N_CAND);
@@ -230,7 +278,8 @@ int main(int argc, char **argv)
     long budget = o.max_templates;
     bool stopped_early = false, wrote_checkpoint = false;
     while (pos < n_templates) {
-        uint32_t n = std::min<uint32_t>(o.chunk, n_templates - pos);
+        /* one round: the next `chunk` templates per device, cut into contiguous pieces, all devices at once */
+        uint32_t n = (uint32_t)std::min<uint64_t>((uint64_t)o.chunk * ndev, n_templates - pos);
         if (budget >= 0) {
             if (budget == 0) {
                 stopped_early = true;
@@ -239,8 +288,11 @@ int main(int argc, char **argv)
             n = (uint32_t)std::min<long>(n, budget);
             budget -= n;
         }
-        CHECK(brp_search_run(s, bank + 3 * (size_t)pos, n, pos));
-        CHECK(brp_search_sync(s));
+        for (size_t d = 0; d < ndev; d++) {
+            const uint32_t lo = (uint32_t)((uint64_t)n * d / ndev), hi = (uint32_t)((uint64_t)n * (d + 1) / ndev);
+            if (hi > lo) CHECK(brp_search_run(handles[d], bank + 3 * (size_t)(pos + lo), hi - lo, pos + lo)); /* asynchronous */
+        }
+        for (size_t d = 0; d < ndev; d++) CHECK(brp_search_sync(handles[d]));
         pos += n;
         const bool last = pos == n_templates;
         const bool due = o.checkpoint && !last && (now_s() - t_last_cp >= o.checkpoint_period_s || budget == 0);
@@ -255,11 +307,12 @@ int main(int argc, char **argv)
     if (budget == 0 && pos < n_templates) stopped_early = true;
     const double t_loop = now_s() - t_start;
     if (o.debug)
-        fprintf(stderr, "%u templates in %.3f s (%.0f templates/s)\n", pos - done, t_loop, (pos - done) / std::max(t_loop, 1e-9));
+        fprintf(stderr, "%u templates on %zu device(s) in %.3f s (%.0f templates/s)\n", pos - done, ndev, t_loop,
+                (pos - done) / std::max(t_loop, 1e-9));
 
     if (stopped_early) {
         fprintf(stderr, "Stopped after %u of %u templates%s.\n", pos, n_templates, wrote_checkpoint ? "; checkpoint written" : "");
-        brp_search_destroy(s);
+        for (brp_search *h : handles) brp_search_destroy(h);
         brp_bank_free(bank);
         return 0;
     }
@@ -269,7 +322,7 @@ int main(int argc, char **argv)
     if (o.checkpoint) CHECK(brp_checkpoint_write(o.checkpoint, n_templates, o.input, merged.data())); /* :1498 final checkpoint */
     CHECK(brp_finalize_candidates(merged.data(), nullptr));
     CHECK(brp_write_candidates(o.output, merged.data(), &g, tsample_us));
-    CHECK(brp_search_destroy(s));
+    for (brp_search *h : handles) CHECK(brp_search_destroy(h));
     brp_bank_free(bank);
     return 0;
 }

@@ -92,6 +92,26 @@ def test_cli_with_whitening_and_zap_list(wu, tag, padding):
     assert len({key(l) for l in got[:-1]} & {key(l) for l in ref[:-1]}) >= 0.9 * (len(ref) - 1)
 
 
+def test_cli_bank_split_over_several_devices_gives_the_same_file(wu):
+    """--devices: one handle per listed device, contiguous pieces of every round of the bank, host merge of the hit lists.
+    The candidate file and the final checkpoint must be byte-identical to the one-device run (an ordinal may repeat, so the
+    split is exercised on a one-GPU box too; with more GPUs visible they are all used)."""
+    import torch
+    run_cli(wu, out="one.cand", cpt="one.cpt")
+    lists = ["0,0,0"]
+    n = torch.cuda.device_count()
+    if n >= 2:
+        lists.append(f"0-{n - 1}")
+    for k, devs in enumerate(lists):
+        r = run_cli(wu, "--devices", devs, "--chunk", "2", out=f"many{k}.cand", cpt=f"many{k}.cpt")
+        assert f"on {len(devs.split(',')) if ',' in devs else n} device(s)" in r.stderr
+        assert (wu / f"many{k}.cand").read_bytes() == (wu / "one.cand").read_bytes()
+        a, b = brp_b200.checkpoint_read(wu / f"many{k}.cpt"), brp_b200.checkpoint_read(wu / "one.cpt")
+        assert a[0] == b[0] and a[2].tobytes() == b[2].tobytes()
+    r = run_cli(wu, "--devices", "0,x", cpt=None, check=False)
+    assert r.returncode == brp_b200.RADPUL_EVAL
+
+
 def test_cli_error_paths(wu):
     run_cli(wu, "--max_templates", "2", "--checkpoint_period", "0")
     (wu / "other.binary").write_bytes((wu / "wu.binary").read_bytes())

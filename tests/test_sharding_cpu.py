@@ -64,6 +64,11 @@ def _worker(rank, world, port, n_templates, fu, w2, q):
     allhits = sharding.gather_hits(mine, dist)
     bank = synth.make_bank(n_templates)
     cands, tidx = brp_b200.toplist_from_hits(allhits, bank)
+    # the production exchange: ONE fixed-size all-gather of the ranks' 5 x 100 strongest per-bin maxima
+    records = sharding.gather_toplists(sharding.local_toplist_records(mine), dist)
+    cands2, tidx2 = brp_b200.toplist_from_hits(records, bank)
+    assert cands2.tobytes() == cands.tobytes() and tidx2.tobytes() == tidx.tobytes()
+    assert len(records) <= 2 * 500
     q.put((rank, lo, hi, len(mine), len(allhits), cands.tobytes(), tidx.tobytes()))
     dist.barrier()
     dist.destroy_process_group()
@@ -75,7 +80,7 @@ def test_two_rank_gloo_shards_merge_to_single_rank_toplist():
     import brp_b200
     from brp_b200 import sharding, synth
 
-    n_templates, fu, w2 = 37, 6866, 100
+    n_templates, fu, w2 = 137, 6866, 100   # enough hits that the per-rank lists overflow 100 entries per harmonic
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -87,7 +92,7 @@ def test_two_rank_gloo_shards_merge_to_single_rank_toplist():
         p.join(timeout=60)
         assert p.exitcode == 0
     (r0, lo0, hi0, n0, tot0, c0, t0), (r1, lo1, hi1, n1, tot1, c1, t1) = results
-    assert (lo0, hi0, lo1, hi1) == (0, 18, 18, 37)              # contiguous, sizes differ by at most one
+    assert (lo0, hi0, lo1, hi1) == (0, 68, 68, 137)             # contiguous, sizes differ by at most one
     assert tot0 == tot1 == n0 + n1
     assert c0 == c1 and t0 == t1                                 # every rank ends with the same merged list
     # single-rank answer
@@ -97,6 +102,30 @@ def test_two_rank_gloo_shards_merge_to_single_rank_toplist():
     assert cands.tobytes() == c0 and tidx.tobytes() == t0
     tie = cands["power"] == np.float32(57.5)
     assert tie.sum() == 5 and np.all(tidx[tie] == 2)             # one per harmonic; earliest of the tied templates (2, 7, 12, ...)
+    assert all(np.count_nonzero(cands["power"][100 * k:100 * k + 100]) == 100 for k in range(5))
+
+
+def test_local_toplist_records_keep_what_the_merge_needs():
+    """numpy restatement of the per-rank reduction against brp_toplist_from_hits on random hit lists with ties"""
+    sys.path.insert(0, str(ROOT))
+    import brp_b200
+    from brp_b200 import sharding, synth
+
+    rng = np.random.default_rng(3)
+    bank = synth.make_bank(50)
+    for trial in range(20):
+        n = int(rng.integers(0, 1500))
+        hits = np.zeros(n, sharding.HIT_DTYPE)
+        hits["power"] = rng.integers(20, 60, n).astype(np.float32)      # few distinct values: many ties
+        hits["bin"] = rng.integers(100, 1100, n)
+        hits["tmpl"] = rng.integers(0, 50, n)
+        hits["harm_idx"] = rng.integers(0, 5, n)
+        rec = sharding.local_toplist_records(hits)
+        a, ta = brp_b200.toplist_from_hits(hits, bank)
+        b, tb = brp_b200.toplist_from_hits(rec[rec["power"] > 0], bank)
+        assert a.tobytes() == b.tobytes() and ta.tobytes() == tb.tobytes()
+        m = a["power"] > 0
+        assert np.array_equal(rec["power"][m], a["power"][m].astype(np.float32)) and np.array_equal(rec["bin"][m], a["f0"][m])
 
 
 def test_shard_ranges_cover_the_bank():
