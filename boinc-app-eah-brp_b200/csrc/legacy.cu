@@ -6,6 +6,16 @@
 // process, single caller thread, set_up_* once in the order resampling -> fft -> harmonic summing, run_*
 // once per template in that order.  This path exists to be a drop-in and a parity proof; throughput
 // numbers come from the batched brp_search_* layer.
+//
+// What keeps the per-template cost down (the interface forces one host round trip per template, nothing forces three):
+//   * run_resampling and run_fft only enqueue; the one synchronisation of a template is in run_harmonic_summing, which is
+//     where the reference driver first looks at results (errors of the earlier kernels surface there);
+//   * the handles passed between the stages are opaque, so the padding is not materialised: run_fft on the buffer of
+//     run_resampling reads n_steps and the mean the resampler left on the device (pad-on-load, as in the batched path);
+//   * nothing of the size of the spectrum crosses the bus or is cleared on the host per template: only the hit list comes
+//     back (a few hundred bytes), sumspec[0..4] and dirty[] hold the values above threshold and zeros elsewhere -- all the
+//     candidate scan reads (demod_binary.c:1350) -- and the entries written for one template are cleared one by one before
+//     the next.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -38,8 +48,10 @@ struct LegacyState {
     brp_hit *d_hits, *h_hits;
     uint32_t *d_hit_counter;
     uint32_t hit_cap;
-    float *h_spectrum; // host copy handed out as sumspec[0]
-    uint32_t fu;
+    float *h_spectrum; // handed out as sumspec[0]: the spectrum's values above threshold, 0 elsewhere
+    uint32_t fu, ps_stride;
+    uint32_t n_prev;   // hits of the previous template, still in h_hits: their entries are cleared before the next fill
+    bool resampled;    // d_resamp holds [0, n_steps) of the current template with d_nsteps / d_mean (padding not written)
 };
 
 LegacyState L;
@@ -131,9 +143,9 @@ int run_resampling(DIfloatPtr input, DIfloatPtr output, const RESAMP_PARAMS *par
     LG_TRY(cudaMemcpyAsync(L.d_tmpl, &t, sizeof(t), cudaMemcpyHostToDevice, L.stream), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     const size_t n4 = ((size_t)g.n + 3) & ~(size_t)3;
     LG_TRY(brp_launch_resample(L.d_series, L.d_tmpl, 1, g, L.d_resamp, n4, NULL, L.d_nsteps, L.d_mean, L.d_partials, L.d_counters,
-                               true, L.stream),
+                               false, L.stream),
            RADPUL_CUDA_KERNEL_INVOKE);
-    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    L.resampled = true;
     return 0;
 }
 
@@ -154,20 +166,23 @@ int set_up_fft(DIfloatPtr input, DIfloatPtr *output, uint32_t nsamples, unsigned
     if (!L.initialised || !output) return RADPUL_EVAL;
     if (fft_size != nsamples / 2 + 1) return RADPUL_EVAL;
     LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
-    int rc = brp_fft_plan_create(&L.plan, nsamples);
+    int rc = brp_fft_plan_create(&L.plan, nsamples, L.gd.nu); // nu: lets pass 1 run as sub-transforms when the upper rows are padding
     if (rc) {
         fprintf(stderr, "[brp_b200] FFT length %u unsupported (2^a or 3*2^a, >= 512 / 1536)\n", nsamples);
         return rc;
     }
     L.have_plan = true;
     LG_TRY(cudaMalloc((void **)&L.d_work, sizeof(float2) * (size_t)L.plan.m), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMalloc((void **)&L.d_ps, sizeof(float) * ((size_t)fft_size + 32)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    // rows of m2 bins, the last one whole, so that pass 2 may store through tensor copies (fft.cu, pass2_tma_map); the
+    // harmonic-summing bulk copies read up to 16 bytes past the last bin they need
+    L.ps_stride = (uint32_t)((((size_t)fft_size + L.plan.m2 - 1) / L.plan.m2 * L.plan.m2 + 64 + 31) & ~(size_t)31);
+    LG_TRY(cudaMalloc((void **)&L.d_ps, sizeof(float) * L.ps_stride), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_nsteps_full, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_mean_zero, sizeof(float)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     const float zero = 0.0f;
     LG_TRY(cudaMemcpy(L.d_nsteps_full, &nsamples, sizeof(uint32_t), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     LG_TRY(cudaMemcpy(L.d_mean_zero, &zero, sizeof(float), cudaMemcpyHostToDevice), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
-    LG_TRY(cudaMemset(L.d_ps, 0, sizeof(float) * ((size_t)fft_size + 32)), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    LG_TRY(cudaMemset(L.d_ps, 0, sizeof(float) * L.ps_stride), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     output->device_ptr = (brp_device_ptr_t) reinterpret_cast<uintptr_t>(L.d_ps);
     return 0;
 }
@@ -176,12 +191,18 @@ int run_fft(DIfloatPtr input, DIfloatPtr output, uint32_t nsamples, unsigned int
 {
     if (!L.initialised || !L.have_plan || nsamples != L.plan.n || as_dev(output) != L.d_ps || !as_dev(input)) return RADPUL_EVAL;
     LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
-    // the legacy caller hands over a fully padded series, so every sample is taken from memory
     const size_t n4 = ((size_t)nsamples + 3) & ~(size_t)3;
-    LG_TRY(brp_launch_fft_power(L.plan, as_dev(input), n4, L.d_nsteps_full, L.d_mean_zero, L.d_work, L.d_ps, (size_t)fft_size + 32,
-                                fft_size, norm_factor, 1, L.stream, NULL),
-           RADPUL_CUDA_FFT_EXEC);
-    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_FFT_EXEC);
+    if (as_dev(input) == L.d_resamp && L.resampled) {
+        // the buffer run_resampling filled: samples [0, n_steps) are there, everything beyond reads as the mean
+        LG_TRY(brp_launch_fft_power(L.plan, L.d_resamp, n4, L.d_nsteps, L.d_mean, L.d_work, L.d_ps, L.ps_stride, fft_size, norm_factor, 1,
+                                    L.stream, NULL, L.gd.nu),
+               RADPUL_CUDA_FFT_EXEC);
+    } else {
+        // some other device buffer: a fully padded series, every sample taken from memory
+        LG_TRY(brp_launch_fft_power(L.plan, as_dev(input), n4, L.d_nsteps_full, L.d_mean_zero, L.d_work, L.d_ps, L.ps_stride, fft_size,
+                                    norm_factor, 1, L.stream, NULL),
+               RADPUL_CUDA_FFT_EXEC);
+    }
     return 0;
 }
 
@@ -219,7 +240,9 @@ int set_up_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int *nr_p
     LG_TRY(cudaMalloc((void **)&L.d_hits, sizeof(brp_hit) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_hit_counter, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMallocHost((void **)&L.h_hits, sizeof(brp_hit) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_HOST);
-    LG_TRY(cudaMallocHost((void **)&L.h_spectrum, sizeof(float) * (fundamental_idx_hi ? fundamental_idx_hi : 1)), RADPUL_CUDA_MEM_ALLOC_HOST);
+    L.h_spectrum = (float *)calloc(fundamental_idx_hi ? fundamental_idx_hi : 1, sizeof(float));
+    if (!L.h_spectrum) return RADPUL_EMEM;
+    L.n_prev = 0;
     return 0;
 }
 
@@ -230,9 +253,16 @@ int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages
     if (!L.initialised || !L.d_keys || !sumspec || !dirty || !thresholds || fundamental_idx_hi != L.fu || !as_dev(powerspectrum))
         return RADPUL_EVAL;
     LG_TRY(cudaSetDevice(L.device), RADPUL_CUDA_DEVICE_SET);
-    // demod_binary_hs_cpu.c:73-83: zero the summed spectra and the page flags, alias sumspec[0] to the spectrum
-    for (int i = 1; i < 5; i++) memset(sumspec[i], 0, fundamental_idx_hi * sizeof(float));
-    for (int i = 0; i < 5; i++) memset(dirty[i], 0, nr_pages * sizeof(int32_t));
+    (void)nr_pages;
+    // demod_binary_hs_cpu.c:73-83 zeroes the summed spectra and the page flags and aliases sumspec[0] to the spectrum; here
+    // the arrays are all-zero except for what the previous template's hits put there, so those entries are cleared instead
+    sumspec[0] = L.h_spectrum;
+    for (uint32_t i = 0; i < L.n_prev; i++) {
+        const brp_hit &h = L.h_hits[i];
+        sumspec[h.harm_idx][h.bin] = 0.0f;
+        dirty[h.harm_idx][h.bin >> BRP_LOG_PS_PAGE_SIZE] = 0;
+    }
+    L.n_prev = 0;
     BrpGeomDev g = L.gd;
     g.w2 = window_2;
     g.fu = fundamental_idx_hi;
@@ -241,22 +271,21 @@ int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages
     for (int k = 0; k < 5; k++) t.t[k] = thresholds[k];
     LG_TRY(cudaMemsetAsync(L.d_keys, 0, sizeof(unsigned long long) * L.hit_cap, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
     LG_TRY(cudaMemsetAsync(L.d_hit_counter, 0, sizeof(uint32_t), L.stream), RADPUL_CUDA_KERNEL_INVOKE);
-    LG_TRY(brp_launch_harmonic_summing(as_dev(powerspectrum), 0, 1, g, t, 0, L.d_keys, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(brp_launch_harmonic_summing(as_dev(powerspectrum), L.ps_stride, 1, g, t, 0, L.d_keys, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
     LG_TRY(brp_launch_collect(L.d_keys, fundamental_idx_hi, 0, L.d_hits, L.hit_cap, L.d_hit_counter, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
     uint32_t n = 0;
     LG_TRY(cudaMemcpyAsync(&n, L.d_hit_counter, sizeof(uint32_t), cudaMemcpyDeviceToHost, L.stream), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
-    LG_TRY(cudaMemcpyAsync(L.h_spectrum, as_dev(powerspectrum), sizeof(float) * fundamental_idx_hi, cudaMemcpyDeviceToHost, L.stream),
-           RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
-    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE); // the one synchronisation of a template
     if (n) {
         LG_TRY(cudaMemcpy(L.h_hits, L.d_hits, sizeof(brp_hit) * n, cudaMemcpyDeviceToHost), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
     }
-    sumspec[0] = L.h_spectrum;
     for (uint32_t i = 0; i < n; i++) {
         const brp_hit &h = L.h_hits[i];
-        if (h.harm_idx > 0) sumspec[h.harm_idx][h.bin] = h.power;
+        sumspec[h.harm_idx][h.bin] = h.power; // harm_idx 0: the spectrum bin itself (P[i] > thr[0], hs_common.c:79)
         dirty[h.harm_idx][h.bin >> BRP_LOG_PS_PAGE_SIZE] = 1;
     }
+    L.n_prev = n;
+    L.resampled = false;
     return 0;
 }
 
@@ -268,7 +297,7 @@ int tear_down_harmonic_summing(float **sumspec, int32_t **dirty)
         for (int i = 0; i < 5; i++) { free(dirty[i]); dirty[i] = NULL; }
     if (!L.initialised) return 0;
     cudaSetDevice(L.device);
-    cudaFree(L.d_keys); cudaFree(L.d_hits); cudaFree(L.d_hit_counter); cudaFreeHost(L.h_hits); cudaFreeHost(L.h_spectrum);
+    cudaFree(L.d_keys); cudaFree(L.d_hits); cudaFree(L.d_hit_counter); cudaFreeHost(L.h_hits); free(L.h_spectrum);
     L.d_keys = NULL; L.d_hits = NULL; L.d_hit_counter = NULL; L.h_hits = NULL; L.h_spectrum = NULL;
     return 0;
 }

@@ -13,7 +13,9 @@
 //   keys       5 x Fu uint64                 per-bin toplist table, lives until brp_search_collect
 //
 // A batch is four kernel launches on one stream (resample, FFT pass 1, FFT pass 2 + power, harmonic sum);
-// nothing is copied back and the host never synchronises inside brp_search_run.
+// nothing is copied back and the host never synchronises inside brp_search_run: the template constants are derived into
+// one of two pinned staging buffers (an event per buffer says when its last upload has left it), so the upload of one
+// call overlaps the kernels of the previous one.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -61,7 +63,9 @@ struct brp_search {
     uint32_t nblk;
     BrpFftPlan plan;
     float *d_series;
-    BrpTemplateDev *d_tmpl, *h_tmpl;
+    BrpTemplateDev *d_tmpl, *h_tmpl[2]; // two pinned staging buffers, used alternately
+    cudaEvent_t ev_tmpl[2];             // recorded behind the upload that read h_tmpl[k]
+    int tmpl_slot;
     uint32_t tmpl_cap;
     float *d_resamp;
     uint32_t *d_nsteps;
@@ -104,7 +108,9 @@ int brp_search_destroy(brp_search *s)
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     brp_fft_plan_destroy(&s->plan);
-    cudaFree(s->d_series); cudaFree(s->d_tmpl); cudaFreeHost(s->h_tmpl); cudaFree(s->d_resamp); cudaFree(s->d_nsteps);
+    cudaFree(s->d_series); cudaFree(s->d_tmpl); cudaFreeHost(s->h_tmpl[0]); cudaFreeHost(s->h_tmpl[1]); cudaFree(s->d_resamp); cudaFree(s->d_nsteps);
+    for (int k = 0; k < 2; k++)
+        if (s->ev_tmpl[k]) cudaEventDestroy(s->ev_tmpl[k]);
     cudaFree(s->d_mean); cudaFree(s->d_partials); cudaFree(s->d_counters); cudaFree(s->d_work); cudaFree(s->d_ps);
     cudaFree(s->d_keys); cudaFree(s->d_hits); cudaFree(s->d_hit_counter); cudaFree(s->d_tap_series);
     cudaFree(s->d_tap_idx); cudaFree(s->d_tap_ps); cudaFree(s->d_tap_keys);
@@ -248,31 +254,50 @@ int brp_search_reset(brp_search *s)
 static int ensure_templates(brp_search *s, uint32_t n)
 {
     if (n <= s->tmpl_cap) return 0;
-    cudaStreamSynchronize(s->stream);
+    cudaStreamSynchronize(s->stream); // growing the buffers: rare (the first call, or a larger chunk than ever before)
     cudaFree(s->d_tmpl);
-    cudaFreeHost(s->h_tmpl);
-    s->d_tmpl = NULL; s->h_tmpl = NULL; s->tmpl_cap = 0;
+    cudaFreeHost(s->h_tmpl[0]);
+    cudaFreeHost(s->h_tmpl[1]);
+    s->d_tmpl = NULL; s->h_tmpl[0] = s->h_tmpl[1] = NULL; s->tmpl_cap = 0;
     const uint32_t cap = n < 1024 ? 1024 : n;
     CU_TRY(cudaMalloc((void **)&s->d_tmpl, sizeof(BrpTemplateDev) * cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    CU_TRY(cudaMallocHost((void **)&s->h_tmpl, sizeof(BrpTemplateDev) * cap), RADPUL_CUDA_MEM_ALLOC_HOST);
+    for (int k = 0; k < 2; k++) {
+        CU_TRY(cudaMallocHost((void **)&s->h_tmpl[k], sizeof(BrpTemplateDev) * cap), RADPUL_CUDA_MEM_ALLOC_HOST);
+        if (!s->ev_tmpl[k]) CU_TRY(cudaEventCreateWithFlags(&s->ev_tmpl[k], cudaEventDisableTiming), RADPUL_CUDA_DEVICE_SET);
+    }
     s->tmpl_cap = cap;
     return 0;
 }
 
-// upload bank[0..n) as device templates; the staging buffer is reused, so wait for earlier work first
+// next pinned staging buffer, free to be overwritten (its last upload has completed; with two buffers that was two calls ago)
+static BrpTemplateDev *staging_acquire(brp_search *s)
+{
+    s->tmpl_slot ^= 1;
+    cudaEventSynchronize(s->ev_tmpl[s->tmpl_slot]); // returns at once for an event that was never recorded
+    return s->h_tmpl[s->tmpl_slot];
+}
+
+// enqueue the upload of the first n staged templates (device buffer: stream order protects the kernels still reading it)
+static int staging_upload(brp_search *s, uint32_t n)
+{
+    CU_TRY(cudaMemcpyAsync(s->d_tmpl, s->h_tmpl[s->tmpl_slot], sizeof(BrpTemplateDev) * n, cudaMemcpyHostToDevice, s->stream),
+           RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    cudaEventRecord(s->ev_tmpl[s->tmpl_slot], s->stream);
+    return 0;
+}
+
+// upload bank[0..n) as device templates, without waiting for the work already enqueued
 static int upload_templates(brp_search *s, const double *bank, uint32_t n)
 {
     int rc = ensure_templates(s, n);
     if (rc) return rc;
-    CU_TRY(cudaStreamSynchronize(s->stream), RADPUL_CUDA_KERNEL_INVOKE);
+    BrpTemplateDev *h = staging_acquire(s);
     for (uint32_t i = 0; i < n; i++) {
         brp_template t;
         brp_derive_template(bank[3 * (size_t)i], bank[3 * (size_t)i + 1], bank[3 * (size_t)i + 2], s->g.step_inv, &t);
-        s->h_tmpl[i].tau = t.tau; s->h_tmpl[i].Omega = t.Omega; s->h_tmpl[i].Psi0 = t.Psi0; s->h_tmpl[i].S0 = t.S0;
+        h[i].tau = t.tau; h[i].Omega = t.Omega; h[i].Psi0 = t.Psi0; h[i].S0 = t.S0;
     }
-    CU_TRY(cudaMemcpyAsync(s->d_tmpl, s->h_tmpl, sizeof(BrpTemplateDev) * n, cudaMemcpyHostToDevice, s->stream),
-           RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
-    return 0;
+    return staging_upload(s, n);
 }
 
 static int run_batch(brp_search *s, const BrpLane &ln, uint32_t first, uint32_t nb, uint32_t first_global,
@@ -406,9 +431,12 @@ int brp_stage_resample(brp_search *s, const brp_template *t, float *resampled_ou
     const size_t nfull = ((size_t)s->g.nsamples + 3) & ~(size_t)3;
     if (!s->d_tap_series) CU_TRY(cudaMalloc((void **)&s->d_tap_series, sizeof(float) * nfull), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     if (!s->d_tap_idx) CU_TRY(cudaMalloc((void **)&s->d_tap_idx, sizeof(int32_t) * s->rs_stride), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    CU_TRY(cudaStreamSynchronize(s->stream), RADPUL_CUDA_KERNEL_INVOKE);
-    s->h_tmpl[0].tau = t->tau; s->h_tmpl[0].Omega = t->Omega; s->h_tmpl[0].Psi0 = t->Psi0; s->h_tmpl[0].S0 = t->S0;
-    CU_TRY(cudaMemcpyAsync(s->d_tmpl, s->h_tmpl, sizeof(BrpTemplateDev), cudaMemcpyHostToDevice, s->stream), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    {
+        BrpTemplateDev *h = staging_acquire(s);
+        h[0].tau = t->tau; h[0].Omega = t->Omega; h[0].Psi0 = t->Psi0; h[0].S0 = t->S0;
+        rc = staging_upload(s, 1);
+        if (rc) return rc;
+    }
     CU_TRY(cudaMemsetAsync(s->d_tap_idx, 0xFF, sizeof(int32_t) * s->rs_stride, s->stream), RADPUL_CUDA_KERNEL_INVOKE);
     CU_TRY(brp_launch_resample(s->d_series, s->d_tmpl, 1, s->gd, s->d_tap_series, nfull, s->d_tap_idx, s->d_nsteps, s->d_mean,
                                s->d_partials, s->d_counters, true, s->stream),
@@ -452,9 +480,9 @@ int brp_stage_resample_compare(brp_search *s, const double *bank, uint32_t n_tem
     for (uint32_t t = 0; t < n_templates && e == cudaSuccess; t++) {
         brp_template bt;
         brp_derive_template(bank[3 * t], bank[3 * t + 1], bank[3 * t + 2], s->g.step_inv, &bt);
-        cudaStreamSynchronize(s->stream); // h_tmpl is reused
-        s->h_tmpl[0].tau = bt.tau; s->h_tmpl[0].Omega = bt.Omega; s->h_tmpl[0].Psi0 = bt.Psi0; s->h_tmpl[0].S0 = bt.S0;
-        e = cudaMemcpyAsync(s->d_tmpl, s->h_tmpl, sizeof(BrpTemplateDev), cudaMemcpyHostToDevice, s->stream);
+        BrpTemplateDev *h = staging_acquire(s);
+        h[0].tau = bt.tau; h[0].Omega = bt.Omega; h[0].Psi0 = bt.Psi0; h[0].S0 = bt.S0;
+        e = staging_upload(s, 1) ? cudaErrorUnknown : cudaSuccess;
         if (e == cudaSuccess) e = cudaMemsetAsync(s->d_tap_idx, 0xFF, sizeof(int32_t) * nu, s->stream);
         if (e == cudaSuccess) e = cudaMemsetAsync(d_idx2, 0xFF, sizeof(int32_t) * nu, s->stream);
         if (e == cudaSuccess)

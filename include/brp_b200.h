@@ -113,10 +113,11 @@ int run_fft(DIfloatPtr input, DIfloatPtr output, uint32_t nsamples, unsigned int
 int tear_down_fft(DIfloatPtr output);
 
 /* cuda/app/demod_binary_hs_cuda.cuh:37-39 / demod_binary_hs_cpu.h:37-61.  sumspec[1..4] and dirty[0..4]
- * are HOST arrays allocated here; after run_harmonic_summing sumspec[0] points at a host copy of the
- * spectrum, dirty[k][page] is set for every page holding a value > thresholds[k], and sumspec[k][j]
- * holds the per-bin maximum for every such value (entries <= threshold are 0 and are never read by
- * the candidate scan, demod_binary.c:1350). */
+ * are HOST arrays allocated here; after run_harmonic_summing sumspec[0] points at a host array of the
+ * spectrum's length up to fundamental_idx_hi, dirty[k][page] is set for every page holding a value
+ * > thresholds[k], and sumspec[k][j] (k = 0..4) holds the per-bin maximum for every such value; all other
+ * entries are 0 and are never selected by the candidate scan (demod_binary.c:1350 tests "> threshold").
+ * run_resampling and run_fft only enqueue work; run_harmonic_summing synchronises and reports their errors. */
 int set_up_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int *nr_pages_ptr, unsigned int fundamental_idx_hi,
                             unsigned int harmonic_idx_hi);
 int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages, DIfloatPtr powerspectrum,

@@ -23,7 +23,7 @@ with tempfile.TemporaryDirectory() as d:
     for n in (8, n_t + 8):          # the difference of two runs removes start-up, ingest and output
         synth.write_bank(d / f"bank{n}.txt", synth.make_bank(n))
     times = {}
-    for n in (8, n_t + 8):
+    for n in (8, 8, n_t + 8):       # the first run pays for loading the CUDA driver and is discarded
         t0 = time.perf_counter()
         r = subprocess.run([str(exe), "-i", str(d / "wu.binary"), "-o", str(d / "o.cand"), "-t", str(d / f"bank{n}.txt"), "-c", str(d / f"c{n}.cpt"),
                             "-f", "400", "-A", "0.08", "-P", "1.0", "-B", "1000", "-D", "0"], capture_output=True, text=True)

@@ -56,21 +56,26 @@ def test_legacy_interface_reproduces_reference_candidates(oracle, golden, tag, p
     # same batched result
     bc, bt = brp_b200.search_bank(series, g, bank, fA=0.08, max_batch=4)
     assert bc.tobytes() == cands.view(brp_b200.CAND_DTYPE).tobytes() and np.array_equal(bt, tidx)
-    # the spectrum handed out as sumspec[0] and the page flags of the last template
-    ss, dd, thrA = taps[-1]
-    t = oracle.template(*bank[-1], go.step_inv)
-    res, _, _, _ = oracle.resample(series, go, t)
-    ps = oracle.power_spectrum(res, go.nsamples)
-    err, _ = power_close(ss[0], ps[: g.fundamental_idx_hi])
-    assert err <= 1e-4
-    rss, rdirty = oracle.harmonic_summing(ps, go, thrA)
-    for k in range(5):
-        ref = ps[: g.fundamental_idx_hi] if k == 0 else rss[k - 1]
-        above = np.nonzero(ref > thrA[k] * np.float32(1.001))[0]
-        assert np.all(dd[k][above >> 10] == 1)
-        if k:
+    # what the driver's candidate scan reads (demod_binary.c:1310-1350): sumspec[0..4] above threshold and the page flags, for
+    # several templates in a row (the arrays are cleared entry by entry between templates, not wholesale)
+    for it in (0, len(bank) // 2, len(bank) - 1):
+        ss, dd, thrA = taps[it]
+        t = oracle.template(*bank[it], go.step_inv)
+        res, _, _, _ = oracle.resample(series, go, t)
+        ps = oracle.power_spectrum(res, go.nsamples)
+        rss, rdirty = oracle.harmonic_summing(ps, go, thrA)
+        for k in range(5):
+            ref = ps[: g.fundamental_idx_hi].copy() if k == 0 else rss[k - 1]
+            if k == 0:
+                ref[: g.window_2] = 0                                   # the summing loop starts at window_2 (hs_common.c:74,79)
+            above = np.nonzero(ref > thrA[k] * np.float32(1.001))[0]
+            assert np.all(dd[k][above >> 10] == 1)
             e, _ = power_close(ss[k][above], ref[above])
             assert e <= 1e-4
+            # nothing else may look like a candidate: every other entry is at or below the threshold
+            rest = np.ones(g.fundamental_idx_hi, bool)
+            rest[np.nonzero(ref > thrA[k] * np.float32(0.999))[0]] = False
+            assert np.all(ss[k][rest] <= thrA[k])
 
 
 def test_legacy_error_codes():

@@ -123,7 +123,7 @@ def _compare_with_reference_run(gr, tag, got_lines, got_cpt, bank):
         if key(l) not in common:
             print("only in this file:         ", l)
     assert got_lines[-1] == "%DONE%" and len(common) >= 0.98 * (len(ref) - 1)
-    assert [key(l) for l in got_lines[:5]] == [key(l) for l in ref[:5]]
+    assert [key(l) for l in got_lines[:-1][:5]] == [key(l) for l in ref[:-1][:5]]
 
 
 def test_reference_bench_command_on_the_real_workunit_64_templates(gr, bank, tmp_path):
