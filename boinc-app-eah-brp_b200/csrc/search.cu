@@ -289,6 +289,7 @@ static int staging_upload(brp_search *s, uint32_t n)
 // upload bank[0..n) as device templates, without waiting for the work already enqueued
 static int upload_templates(brp_search *s, const double *bank, uint32_t n)
 {
+    if (n == 0) return 0; // an empty bank: nothing to stage
     int rc = ensure_templates(s, n);
     if (rc) return rc;
     BrpTemplateDev *h = staging_acquire(s);

@@ -30,4 +30,21 @@ with tempfile.TemporaryDirectory() as d:
         times[n] = time.perf_counter() - t0
         assert r.returncode == 0, r.stderr[-1000:]
     dt = times[n_t + 8] - times[8]
-    print(f"legacy drop-in path: {n_t} templates in {dt:.2f} s = {n_t / dt:.0f} templates/s (whole runs: {times})")
+    print(f"unmodified reference driver on this backend: {n_t} templates in {dt:.2f} s = {n_t / dt:.0f} templates/s (whole runs: {times}); "
+          "the standalone (non-BOINC) driver writes its checkpoint file after EVERY template (demod_binary.c:1423-1427), which bounds this rate")
+
+# the backend alone: the eleven legacy functions called in the driver's order from this process (no driver, no checkpoint file)
+g = brp_b200.derive_geometry(1 << 22, synth.TSAMPLE_US, 1.0, 400.0, 1000)
+be = brp_b200.LegacyBackend()
+be.set_up(series, g)
+thr = brp_b200.base_thresholds(0.08, g.fft_size)
+bank = synth.make_bank(n_t + 20)
+for row in bank[:20]:
+    be.run_template(brp_b200.derive_template(*row, g.step_inv), thr)
+t0 = time.perf_counter()
+for row in bank[20:]:
+    be.run_template(brp_b200.derive_template(*row, g.step_inv), thr)
+dt = time.perf_counter() - t0
+be.shutdown()
+print(f"legacy backend functions alone (run_resampling + run_fft + run_harmonic_summing per template, ctypes caller): "
+      f"{n_t} templates in {dt:.3f} s = {n_t / dt:.0f} templates/s")
