@@ -190,22 +190,20 @@ def stage_report(brp_b200, s, shard, g, nb, peak):
     """CUDA events around each stage of one batch, on the library's stream; fractions = algorithmic bytes / time / HBM peak."""
     alg = algorithmic_bytes(g)
     ms = [float(x) for x in s.profile_batch(shard, nb, repeats=5)]
-    fused = bool(getattr(s, "fused", False))
     front_ms = ms[0] + ms[1] + ms[2]
     stages = {
-        # resampling and FFT are one fused front end when `fused`: the gather happens inside FFT pass 1's load, so the
-        # two stages can only be timed (and held against their summed algorithmic bytes) together
-        "resample_fft_power": {"ms_per_batch": front_ms, "prep_ms": ms[0], "pass1_ms": ms[1], "pass2_ms": ms[2],
-                               "GBps": (alg["resample"] + alg["fft_power"]) * nb / (front_ms * 1e-3) / 1e9},
+        "resample": {"ms_per_batch": ms[0], "GBps": alg["resample"] * nb / (ms[0] * 1e-3) / 1e9},
+        "fft_power": {"ms_per_batch": ms[1] + ms[2], "pass1_ms": ms[1], "pass2_ms": ms[2],
+                      "GBps": alg["fft_power"] * nb / ((ms[1] + ms[2]) * 1e-3) / 1e9},
         "harmonic_sum": {"ms_per_batch": ms[3], "GBps": alg["harmonic_sum"] * nb / (ms[3] * 1e-3) / 1e9},
+        # the front end as a whole (what a fusion of the resampler into the FFT would be held against): not a candidate for
+        # the dominant stage, the three above are
+        "resample_fft_power": {"ms_per_batch": front_ms, "resample_ms": ms[0], "pass1_ms": ms[1], "pass2_ms": ms[2],
+                               "GBps": (alg["resample"] + alg["fft_power"]) * nb / (front_ms * 1e-3) / 1e9},
     }
-    if not fused:
-        stages["resample"] = {"ms_per_batch": ms[0], "GBps": alg["resample"] * nb / (ms[0] * 1e-3) / 1e9}
-        stages["fft_power"] = {"ms_per_batch": ms[1] + ms[2], "pass1_ms": ms[1], "pass2_ms": ms[2],
-                               "GBps": alg["fft_power"] * nb / ((ms[1] + ms[2]) * 1e-3) / 1e9}
     for v in stages.values():
         v["frac"] = v["GBps"] / peak
-    return alg, stages, fused
+    return alg, stages
 
 
 def other_config(brp_b200, synth, log2n, padding, n_handles, templates, batch, peak, device):
@@ -234,7 +232,7 @@ def other_config(brp_b200, synth, log2n, padding, n_handles, templates, batch, p
         h.sync()
     dt = time.perf_counter() - t0
     dev_ms = max(h.last_run_ms() for h in handles)
-    alg, stages, _ = stage_report(brp_b200, handles[0], bank, g, min(batch, templates), peak)
+    alg, stages = stage_report(brp_b200, handles[0], bank, g, min(batch, templates), peak)
     for h in handles:
         h.close()
     value = templates * n_handles * steps / dt
@@ -312,15 +310,24 @@ def run_ours(args):
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
     value = n_total * args.steps / (dev_ms * 1e-3)
 
-    # ---- end to end through the C ABI with host buffers (series + bank in, hits out, one exchange, host merge)
+    # ---- end to end through the C ABI with host buffers (series + bank in, hits out, one exchange, host merge).
+    # Two handles alternate, as a driver with a queue of work-units would use them: the upload of step k+1's series overlaps the
+    # search of step k, and step k's read-back, exchange and host merge overlap the search of step k+1.  Every step still
+    # uploads its own series and bank from (pinned) host memory and reads its own hit list back.
+    s2 = brp_b200.Search(g, fA=FA, max_batch=args.batch, device=local)
+    handles = [s, s2]
     hit_bytes = 0
 
-    def e2e_step():
+    def begin(h):
+        h.reset()
+        h.set_series_ptr(pinned.data_ptr())            # H2D of the work-unit from pinned host memory (asynchronous)
+
+    def launch(h):
+        h.run(shard, lo)                               # derives template constants on the host, H2D, enqueues all batches
+
+    def finish(h):
         nonlocal hit_bytes
-        s.reset()
-        s.set_series_ptr(pinned.data_ptr())            # H2D of the work-unit from pinned host memory
-        s.run(shard, lo)                               # derives template constants on the host, H2D, enqueues all batches
-        hits = s.collect()                             # D2H of the compacted per-bin maxima of this shard
+        hits = h.collect()                             # D2H of the compacted per-bin maxima of this shard
         hit_bytes = hits.nbytes + 4
         # the single exchange of the search: ONE fixed-size all-gather (5 x 100 records per rank) over NCCL
         records = sharding.gather_toplists(sharding.local_toplist_records(hits), dist, torch.device("cuda", local))
@@ -328,14 +335,28 @@ def run_ours(args):
             return brp_b200.toplist_from_hits(records, bank)
         return None
 
-    e2e_step()
+    def e2e_steps(n):
+        top = None
+        begin(handles[0])
+        launch(handles[0])
+        for k in range(n):
+            cur, nxt = handles[k % 2], handles[(k + 1) % 2]
+            if k + 1 < n:
+                begin(nxt)
+            cur.sync()
+            if k + 1 < n:
+                launch(nxt)
+            top = finish(cur)
+        return top
+
+    e2e_steps(2)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        top = e2e_step()
+    top = e2e_steps(args.steps)
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = n_total * args.steps / e2e_s
+    s2.close()
 
     # ---- secondary: weak scaling (every GPU searches the whole bank), for comparison with round 1's records
     weak = None
@@ -353,23 +374,21 @@ def run_ours(args):
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
         nb = min(args.batch, len(shard))
-        alg, stages, fused = stage_report(brp_b200, s, shard, g, nb, peak)
-        dom = max((k for k in stages if k not in ("resample", "fft_power")) if fused else ("resample", "fft_power", "harmonic_sum"),
-                  key=lambda k: stages[k]["ms_per_batch"])
+        alg, stages = stage_report(brp_b200, s, shard, g, nb, peak)
+        dom = max(("resample", "fft_power", "harmonic_sum"), key=lambda k: stages[k]["ms_per_batch"])
         # DRAM bytes per launch of the dominant stage, from the committed ncu --set full capture (same batch size only)
         traffic = None
-        tpath = ROOT / "profiles" / ("r2_traffic.json" if fused else "r1_traffic.json")
+        tpath = ROOT / "profiles" / "r2_traffic.json"
         if tpath.exists() and args.log2n == 22 and args.padding == 1.0:
             t = json.loads(tpath.read_text())
             if t.get("batch") == nb:
                 traffic = t["dram_bytes_per_launch"].get(dom)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["GBps"], "peak": peak, "peak_source": peak_src,
                     "unit": "GB/s", "frac": stages[dom]["GBps"] / peak, "traffic": traffic,
-                    "algorithmic_bytes_per_template": alg, "templates_per_launch": nb, "fused_resample_into_fft": fused, "stages": stages,
-                    "note": "stage fractions are algorithmic bytes / CUDA-event time / HBM peak. With the resampling gather fused into "
-                            "FFT pass 1 the stage 'resample_fft_power' covers both reference stages (prep kernel + pass 1 + pass 2) and "
-                            "is held against the SUM of their algorithmic bytes (SURVEY.md 8d: fusions are reported, the denominator is "
-                            "not redefined)",
+                    "algorithmic_bytes_per_template": alg, "templates_per_launch": nb, "stages": stages,
+                    "note": "stage fractions are algorithmic bytes / CUDA-event time / HBM peak; the resampler's 4*Nu input bytes per template "
+                            "come from L2 (the series is shared by the batch), so its fraction can exceed 1; 'resample_fft_power' is the front "
+                            "end as a whole against the sum of its two stages' bytes",
                     "whole_loop": {"GBps": alg["total"] * value / world / 1e9, "frac": alg["total"] * value / world / 1e9 / peak,
                                    "note": "per GPU"}}
         cpu = None
@@ -403,6 +422,7 @@ def run_ours(args):
             "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(series.nbytes + 16 * len(shard)),
                     "d2h_bytes_per_step": int(hit_bytes), "ms_per_step": 1e3 * e2e_s / args.steps,
+                    "pipelining": "two handles alternate: step k+1's upload overlaps step k's search, step k's read-back and merge overlap step k+1's search",
                     "exchange": "one all-gather of 8 000 bytes per rank" if world > 1 else "none (one GPU)"},
             "gpu_launches": int(launches),
         }

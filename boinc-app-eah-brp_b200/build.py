@@ -62,7 +62,7 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     if force or _stale(CLI, [main, LIB, (CSRC / "../../include/brp_b200.h").resolve()]):
         cxx = os.environ.get("CXX", "g++")
         subprocess.run([cxx, "-O2", "-std=c++17", str(main), "-o", str(CLI), f"-L{HERE}", "-lbrp_b200",
-                        "-Wl,-rpath,$ORIGIN", "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"], check=True)
+                        "-Wl,-rpath,$ORIGIN", "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64", "-pthread"], check=True)
     return LIB
 
 

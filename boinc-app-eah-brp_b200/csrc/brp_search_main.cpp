@@ -21,6 +21,7 @@
 #include <time.h>
 
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 #include "../../include/brp_b200.h"
@@ -288,11 +289,22 @@ int main(int argc, char **argv)
             n = (uint32_t)std::min<long>(n, budget);
             budget -= n;
         }
-        for (size_t d = 0; d < ndev; d++) {
+        /* one host thread per device enqueues (and awaits) that device's piece: the first launches on a device load its kernels,
+         * which takes milliseconds and would otherwise be paid device after device */
+        std::vector<int> rcs(ndev, 0);
+        auto piece = [&](size_t d) {
             const uint32_t lo = (uint32_t)((uint64_t)n * d / ndev), hi = (uint32_t)((uint64_t)n * (d + 1) / ndev);
-            if (hi > lo) CHECK(brp_search_run(handles[d], bank + 3 * (size_t)(pos + lo), hi - lo, pos + lo)); /* asynchronous */
+            if (hi > lo) rcs[d] = brp_search_run(handles[d], bank + 3 * (size_t)(pos + lo), hi - lo, pos + lo); /* asynchronous */
+            if (!rcs[d]) rcs[d] = brp_search_sync(handles[d]);
+        };
+        if (ndev == 1) {
+            piece(0);
+        } else {
+            std::vector<std::thread> workers;
+            for (size_t d = 0; d < ndev; d++) workers.emplace_back(piece, d);
+            for (std::thread &w : workers) w.join();
         }
-        for (size_t d = 0; d < ndev; d++) CHECK(brp_search_sync(handles[d]));
+        for (size_t d = 0; d < ndev; d++) CHECK(rcs[d]);
         pos += n;
         const bool last = pos == n_templates;
         const bool due = o.checkpoint && !last && (now_s() - t_last_cp >= o.checkpoint_period_s || budget == 0);

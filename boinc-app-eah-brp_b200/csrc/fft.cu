@@ -998,18 +998,17 @@ typedef CUresult (*tensor_map_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuu
 
 static tensor_map_encode_fn tensor_map_encoder()
 {
-    static tensor_map_encode_fn fn = nullptr;
-    static bool looked = false;
-    if (!looked) {
-        looked = true;
+    // looked up once (a function-local static is initialised exactly once even when several host threads, one per device,
+    // enqueue their first batch at the same time)
+    static const tensor_map_encode_fn fn = []() -> tensor_map_encode_fn {
         const char *off = getenv("BRP_FFT_TMA"); // BRP_FFT_TMA=0 selects the plain kernel (A/B measurements)
-        if (!(off && off[0] == '0')) {
-            void *sym = nullptr;
-            cudaDriverEntryPointQueryResult q;
-            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-                fn = (tensor_map_encode_fn)sym;
-        }
-    }
+        if (off && off[0] == '0') return nullptr;
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            return (tensor_map_encode_fn)sym;
+        return nullptr;
+    }();
     return fn;
 }
 

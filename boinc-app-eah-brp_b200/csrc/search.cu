@@ -325,18 +325,38 @@ int brp_search_run(brp_search *s, const double *bank, uint32_t n_templates, uint
 {
     if (!s || (!bank && n_templates)) return RADPUL_EVAL;
     CU_TRY(cudaSetDevice(s->device), RADPUL_CUDA_DEVICE_SET);
-    int rc = upload_templates(s, bank, n_templates);
-    if (rc) return rc;
+    int rc = 0;
+    if (s->n_lanes > 1) {
+        rc = upload_templates(s, bank, n_templates);
+        if (rc) return rc;
+    } else if (n_templates) {
+        rc = ensure_templates(s, n_templates);
+        if (rc) return rc;
+    }
     cudaEventRecord(s->ev_start, s->stream);
     // fork: the other lanes start after everything already queued on the handle's stream (series, templates, reset)
     cudaEventRecord(s->ev_fork, s->stream);
     for (int l = 1; l < s->n_lanes; l++) cudaStreamWaitEvent(s->lane[l].st, s->ev_fork, 0);
+    // One lane (the default): the constants of a batch are derived and uploaded right before its kernels are enqueued, so the
+    // GPU starts on the first batch while the host is still deriving the rest of the bank (6 662 templates take half a
+    // millisecond of host time, which matters once the bank is split over eight GPUs).
+    BrpTemplateDev *h = (s->n_lanes == 1 && n_templates) ? staging_acquire(s) : NULL;
     uint32_t k = 0;
     for (uint32_t first = 0; first < n_templates; first += s->max_batch, k++) {
         const uint32_t nb = n_templates - first < s->max_batch ? n_templates - first : s->max_batch;
+        if (h) {
+            for (uint32_t i = first; i < first + nb; i++) {
+                brp_template t;
+                brp_derive_template(bank[3 * (size_t)i], bank[3 * (size_t)i + 1], bank[3 * (size_t)i + 2], s->g.step_inv, &t);
+                h[i].tau = t.tau; h[i].Omega = t.Omega; h[i].Psi0 = t.Psi0; h[i].S0 = t.S0;
+            }
+            CU_TRY(cudaMemcpyAsync(s->d_tmpl + first, h + first, sizeof(BrpTemplateDev) * nb, cudaMemcpyHostToDevice, s->stream),
+                   RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+        }
         rc = run_batch(s, s->lane[k % s->n_lanes], first, nb, first_global_index, s->d_keys, NULL);
         if (rc) return rc;
     }
+    if (h) cudaEventRecord(s->ev_tmpl[s->tmpl_slot], s->stream); // the staging buffer is free again once the last upload has left it
     // join: the handle's stream continues only after every lane has drained
     for (int l = 1; l < s->n_lanes; l++) {
         cudaEventRecord(s->lane[l].done, s->lane[l].st);

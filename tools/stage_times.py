@@ -16,5 +16,5 @@ d = json.loads(lines[-1])
 st = d["roofline"]["stages"]
 front = st["resample_fft_power"]
 print(f"value {d['value']:.0f}  e2e {d['e2e']['value']:.0f}  batch {d['config']['batch']}  cands {d['config']['candidates_found']}  "
-      f"fused {d['roofline']['fused_resample_into_fft']}  prep/resample {front['prep_ms'] * 1e3:.1f}  pass1 {front['pass1_ms'] * 1e3:.1f}  "
+      f"resample {front['resample_ms'] * 1e3:.1f}  pass1 {front['pass1_ms'] * 1e3:.1f}  "
       f"pass2 {front['pass2_ms'] * 1e3:.1f}  hs {st['harmonic_sum']['ms_per_batch'] * 1e3:.1f} us")
