@@ -42,6 +42,17 @@ cudaError_t brp_launch_sin_lut(const float *x, float *out, uint32_t n, cudaStrea
 cudaError_t brp_launch_round_index(const float *f, int32_t *out, uint32_t n, cudaStream_t st);
 
 // ---------------- FFT + power spectrum (fft.cu) ----------------
+// tensor maps of the last launch, kept per plan (= per handle): a search launches every batch on the same buffers, so the three
+// cuTensorMapEncodeTiled calls happen once per handle (and once more for a shorter last batch), not once per batch
+struct BrpFftMapCache {
+    const void *in, *work, *out;
+    size_t in_stride, out_stride;
+    uint32_t bound, count;
+    int batch1, batch2, parts;
+    bool valid1, valid2, ok2;
+    unsigned char in_map[128], out_map[128], ps_map[128]; // copied with memcpy (the handle comes from calloc: no 64-byte alignment)
+};
+
 struct BrpFftPlan {
     uint32_t n;      // real length
     uint32_t m;      // complex length n/2
@@ -58,6 +69,7 @@ struct BrpFftPlan {
     float2 *tw_parts, *tw_inter_parts;
     int smem_pass1, smem_pass2;
     int launches_per_batch;
+    mutable BrpFftMapCache maps;
 };
 
 // nu_hint: number of samples that can be valid (Nu) if the caller knows it, else 0; it may move the split of m so that

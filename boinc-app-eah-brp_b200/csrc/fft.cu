@@ -1098,8 +1098,21 @@ static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, si
 {
     const TileInfo *t1 = find_tile(p.m2), *t2 = find_tile(p.m1);
     const dim3 g1((p.m1 + t1->rows - 1) / t1->rows, batch);
+    static_assert(sizeof(CUtensorMap) == 128, "BrpFftMapCache stores tensor maps as 128 bytes");
     CUtensorMap in_map, out_map;
-    const int parts = pass1_tma_maps(p, in, in_stride, work, batch, n_steps_bound, &in_map, &out_map);
+    BrpFftMapCache &mc = p.maps;
+    int parts;
+    if (mc.valid1 && mc.in == in && mc.in_stride == in_stride && mc.work == work && mc.batch1 == batch && mc.bound == n_steps_bound) {
+        parts = mc.parts;
+        memcpy(&in_map, mc.in_map, 128);
+        memcpy(&out_map, mc.out_map, 128);
+    } else {
+        parts = pass1_tma_maps(p, in, in_stride, work, batch, n_steps_bound, &in_map, &out_map);
+        mc.in = in; mc.in_stride = in_stride; mc.work = work; mc.batch1 = batch; mc.bound = n_steps_bound; mc.parts = parts;
+        memcpy(mc.in_map, &in_map, 128);
+        memcpy(mc.out_map, &out_map, 128);
+        mc.valid1 = true;
+    }
     const int tma_smem = Layout<kTmaL, kTmaRows, 3>::BYTES;
     const dim3 gp(p.m1 / kTmaRows, batch, parts > 0 ? parts : 1);
     if (parts == 1)
@@ -1118,7 +1131,19 @@ static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, si
     const int T2 = t2->rows / 2;
     const dim3 g2((p.m2 / 2 + 1 + T2 - 1) / T2, batch); // rows k2 = 0 .. m2/2
     CUtensorMap ps_map;
-    if (mode == PASS2_POWER && pass2_tma_map(p, out, out_stride, out_count, batch, &ps_map)) {
+    bool tma2 = false;
+    if (mode == PASS2_POWER) {
+        if (mc.valid2 && mc.out == out && mc.out_stride == out_stride && mc.count == out_count && mc.batch2 == batch) {
+            tma2 = mc.ok2;
+            memcpy(&ps_map, mc.ps_map, 128);
+        } else {
+            tma2 = pass2_tma_map(p, out, out_stride, out_count, batch, &ps_map);
+            mc.out = out; mc.out_stride = out_stride; mc.count = out_count; mc.batch2 = batch; mc.ok2 = tma2;
+            memcpy(mc.ps_map, &ps_map, 128);
+            mc.valid2 = true;
+        }
+    }
+    if (tma2) {
         fft_pass2_tma_kernel<<<g2, 256, Layout<1024, 8, 2>::BYTES, st>>>(ps_map, work, out, out_stride, out_count, p.m2, p.m, norm,
                                                                        p.tw_pass2, p.tw_untangle_a, p.tw_untangle_b);
         return cudaGetLastError();
