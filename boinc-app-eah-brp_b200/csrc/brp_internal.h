@@ -100,4 +100,8 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
 cudaError_t brp_launch_collect(const unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits,
                                uint32_t max_hits, uint32_t *counter, cudaStream_t st);
 
+// the same, and every non-empty entry is zeroed behind the scan (the table is empty again afterwards)
+cudaError_t brp_launch_collect_and_clear(unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits, uint32_t max_hits,
+                                         uint32_t *counter, cudaStream_t st);
+
 #endif

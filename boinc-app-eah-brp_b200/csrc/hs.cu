@@ -221,13 +221,15 @@ harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomD
 #undef BRP_HS_STEP
 }
 
-__global__ void collect_kernel(const unsigned long long *__restrict__ keys, uint32_t fu, uint32_t w2,
-                               brp_hit *__restrict__ hits, uint32_t max_hits, uint32_t *__restrict__ counter)
+// clear: leave the table empty behind the scan (one-template-per-call callers: saves them a memset of the whole table per call)
+__global__ void collect_kernel(unsigned long long *__restrict__ keys, uint32_t fu, uint32_t w2,
+                               brp_hit *__restrict__ hits, uint32_t max_hits, uint32_t *__restrict__ counter, bool clear)
 {
     const uint32_t total = 5u * fu;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
         const unsigned long long key = keys[e];
         if (key == 0ull) continue;
+        if (clear) keys[e] = 0ull;
         const uint32_t k = e / fu, bin = e - k * fu;
         if (bin < w2) continue; // the candidate scan starts at window_2 (demod_binary.c:1323)
         const uint32_t slot = atomicAdd(counter, 1u);
@@ -276,6 +278,13 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
 cudaError_t brp_launch_collect(const unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits,
                                uint32_t max_hits, uint32_t *counter, cudaStream_t st)
 {
-    collect_kernel<<<296, 256, 0, st>>>(keys, fu, w2, hits, max_hits, counter);
+    collect_kernel<<<296, 256, 0, st>>>(const_cast<unsigned long long *>(keys), fu, w2, hits, max_hits, counter, false);
+    return cudaGetLastError();
+}
+
+cudaError_t brp_launch_collect_and_clear(unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits, uint32_t max_hits,
+                                         uint32_t *counter, cudaStream_t st)
+{
+    collect_kernel<<<296, 256, 0, st>>>(keys, fu, w2, hits, max_hits, counter, true);
     return cudaGetLastError();
 }

@@ -45,12 +45,13 @@ struct LegacyState {
     float *d_mean_zero;
     // harmonic summing
     unsigned long long *d_keys;
-    brp_hit *d_hits, *h_hits;
-    uint32_t *d_hit_counter;
+    // device: [counter (one brp_hit-sized slot)][hits ...], so that the counter and the first kLegacyFirstHits hits come back
+    // in ONE copy; host mirror in pinned memory
+    brp_hit *d_hitbuf, *h_hitbuf;
     uint32_t hit_cap;
     float *h_spectrum; // handed out as sumspec[0]: the spectrum's values above threshold, 0 elsewhere
     uint32_t fu, ps_stride;
-    uint32_t n_prev;   // hits of the previous template, still in h_hits: their entries are cleared before the next fill
+    uint32_t n_prev;   // hits of the previous template, still in h_hitbuf: their entries are cleared before the next fill
     bool resampled;    // d_resamp holds [0, n_steps) of the current template with d_nsteps / d_mean (padding not written)
 };
 
@@ -66,6 +67,8 @@ LegacyState L;
     } while (0)
 
 inline float *as_dev(DIfloatPtr p) { return reinterpret_cast<float *>(p.device_ptr); }
+
+constexpr uint32_t kLegacyFirstHits = 255; // with the counter slot: one 4 KB transfer covers nearly every template
 
 } // namespace
 
@@ -237,9 +240,10 @@ int set_up_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int *nr_p
     L.fu = fundamental_idx_hi;
     L.hit_cap = 5u * (fundamental_idx_hi ? fundamental_idx_hi : 1u);
     LG_TRY(cudaMalloc((void **)&L.d_keys, sizeof(unsigned long long) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMalloc((void **)&L.d_hits, sizeof(brp_hit) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMalloc((void **)&L.d_hit_counter, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMallocHost((void **)&L.h_hits, sizeof(brp_hit) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_HOST);
+    LG_TRY(cudaMalloc((void **)&L.d_hitbuf, sizeof(brp_hit) * ((size_t)L.hit_cap + 1)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMallocHost((void **)&L.h_hitbuf, sizeof(brp_hit) * ((size_t)L.hit_cap + 1)), RADPUL_CUDA_MEM_ALLOC_HOST);
+    // the per-bin table starts empty and is left empty by every run_harmonic_summing (the collecting kernel clears what it reads)
+    LG_TRY(cudaMemset(L.d_keys, 0, sizeof(unsigned long long) * L.hit_cap), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     L.h_spectrum = (float *)calloc(fundamental_idx_hi ? fundamental_idx_hi : 1, sizeof(float));
     if (!L.h_spectrum) return RADPUL_EMEM;
     L.n_prev = 0;
@@ -258,7 +262,7 @@ int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages
     // the arrays are all-zero except for what the previous template's hits put there, so those entries are cleared instead
     sumspec[0] = L.h_spectrum;
     for (uint32_t i = 0; i < L.n_prev; i++) {
-        const brp_hit &h = L.h_hits[i];
+        const brp_hit &h = L.h_hitbuf[1 + i];
         sumspec[h.harm_idx][h.bin] = 0.0f;
         dirty[h.harm_idx][h.bin >> BRP_LOG_PS_PAGE_SIZE] = 0;
     }
@@ -269,18 +273,22 @@ int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages
     g.h = harmonic_idx_hi;
     BrpThresholds t;
     for (int k = 0; k < 5; k++) t.t[k] = thresholds[k];
-    LG_TRY(cudaMemsetAsync(L.d_keys, 0, sizeof(unsigned long long) * L.hit_cap, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
-    LG_TRY(cudaMemsetAsync(L.d_hit_counter, 0, sizeof(uint32_t), L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    uint32_t *const d_counter = reinterpret_cast<uint32_t *>(L.d_hitbuf);
+    LG_TRY(cudaMemsetAsync(d_counter, 0, sizeof(uint32_t), L.stream), RADPUL_CUDA_KERNEL_INVOKE);
     LG_TRY(brp_launch_harmonic_summing(as_dev(powerspectrum), L.ps_stride, 1, g, t, 0, L.d_keys, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
-    LG_TRY(brp_launch_collect(L.d_keys, fundamental_idx_hi, 0, L.d_hits, L.hit_cap, L.d_hit_counter, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
-    uint32_t n = 0;
-    LG_TRY(cudaMemcpyAsync(&n, L.d_hit_counter, sizeof(uint32_t), cudaMemcpyDeviceToHost, L.stream), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
+    LG_TRY(brp_launch_collect_and_clear(L.d_keys, fundamental_idx_hi, 0, L.d_hitbuf + 1, L.hit_cap, d_counter, L.stream),
+           RADPUL_CUDA_KERNEL_INVOKE);
+    LG_TRY(cudaMemcpyAsync(L.h_hitbuf, L.d_hitbuf, sizeof(brp_hit) * (1 + kLegacyFirstHits), cudaMemcpyDeviceToHost, L.stream),
+           RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
     LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE); // the one synchronisation of a template
-    if (n) {
-        LG_TRY(cudaMemcpy(L.h_hits, L.d_hits, sizeof(brp_hit) * n, cudaMemcpyDeviceToHost), RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
+    const uint32_t n = *reinterpret_cast<const uint32_t *>(L.h_hitbuf);
+    if (n > kLegacyFirstHits) { // rare: more hits than the first transfer holds
+        LG_TRY(cudaMemcpy(L.h_hitbuf + 1 + kLegacyFirstHits, L.d_hitbuf + 1 + kLegacyFirstHits, sizeof(brp_hit) * (n - kLegacyFirstHits),
+                          cudaMemcpyDeviceToHost),
+               RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
     }
     for (uint32_t i = 0; i < n; i++) {
-        const brp_hit &h = L.h_hits[i];
+        const brp_hit &h = L.h_hitbuf[1 + i];
         sumspec[h.harm_idx][h.bin] = h.power; // harm_idx 0: the spectrum bin itself (P[i] > thr[0], hs_common.c:79)
         dirty[h.harm_idx][h.bin >> BRP_LOG_PS_PAGE_SIZE] = 1;
     }
@@ -297,8 +305,8 @@ int tear_down_harmonic_summing(float **sumspec, int32_t **dirty)
         for (int i = 0; i < 5; i++) { free(dirty[i]); dirty[i] = NULL; }
     if (!L.initialised) return 0;
     cudaSetDevice(L.device);
-    cudaFree(L.d_keys); cudaFree(L.d_hits); cudaFree(L.d_hit_counter); cudaFreeHost(L.h_hits); free(L.h_spectrum);
-    L.d_keys = NULL; L.d_hits = NULL; L.d_hit_counter = NULL; L.h_hits = NULL; L.h_spectrum = NULL;
+    cudaFree(L.d_keys); cudaFree(L.d_hitbuf); cudaFreeHost(L.h_hitbuf); free(L.h_spectrum);
+    L.d_keys = NULL; L.d_hitbuf = NULL; L.h_hitbuf = NULL; L.h_spectrum = NULL;
     return 0;
 }
 

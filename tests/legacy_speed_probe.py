@@ -14,7 +14,7 @@ sys.path.insert(0, str(ROOT))
 import brp_b200  # noqa: E402,F401
 from brp_b200 import synth  # noqa: E402
 
-n_t = int(sys.argv[1]) if len(sys.argv) > 1 else 400
+n_t = int(sys.argv[1]) if len(sys.argv) > 1 else 3000
 exe = ROOT / "oracle" / "_ref" / "demod_binary_b200"
 with tempfile.TemporaryDirectory() as d:
     d = Path(d)
@@ -31,7 +31,8 @@ with tempfile.TemporaryDirectory() as d:
         assert r.returncode == 0, r.stderr[-1000:]
     dt = times[n_t + 8] - times[8]
     print(f"unmodified reference driver on this backend: {n_t} templates in {dt:.2f} s = {n_t / dt:.0f} templates/s (whole runs: {times}); "
-          "the standalone (non-BOINC) driver writes its checkpoint file after EVERY template (demod_binary.c:1423-1427), which bounds this rate")
+          "includes the driver's own per-template work: the standalone (non-BOINC) driver writes its checkpoint file after EVERY "
+          "template (demod_binary.c:1423-1427), so this figure depends on the file system under the temporary directory")
 
 # the backend alone: the eleven legacy functions called in the driver's order from this process (no driver, no checkpoint file)
 g = brp_b200.derive_geometry(1 << 22, synth.TSAMPLE_US, 1.0, 400.0, 1000)
