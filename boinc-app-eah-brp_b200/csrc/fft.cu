@@ -96,16 +96,21 @@ __host__ __device__ constexpr int cfg_tw_size(int L) { return cfg_tw_offset(L, c
 // chosen per tile shape with tools/bank_conflicts.py, which replays every shared-memory access of the transform:
 // with these values all stages of the production shapes are conflict-free (pass 1: 2048x4, pass 2: 1024x8 incl.
 // the digit-reversed reads of the untangle epilogue).
+#ifndef BRP_FFT_P1_LAYOUT
+#define BRP_FFT_P1_LAYOUT 2 // 1: the round-1 layout of the tensor-copy pass 1 (2-way conflicts in the dense stage-0 read), for A/B runs
+#endif
 template <int L, int ROWS, int PASS>
 struct Layout {
     // the radix-32 plans (L = 1024: 32x32, L = 512: 32x16) pad every 32 (resp. 16) positions
     static constexpr int C4 = (L == 1024 || (L == 512 && PASS == 1)) ? 0 : 1;
     static constexpr int C5 = (L == 1024) ? 1 : 0;
     static constexpr int C8 = ((PASS == 2 && (L == 2048 || L == 4096)) || PASS == 3) ? 1 : 0; // PASS 3: pass 1 through TMA, see below
-    static constexpr int EXTRA = PASS == 3 ? 2 : PASS == 2 ? (L == 2048 ? (ROWS == 8 ? 2 : 4) : L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
+    static constexpr int EXTRA = PASS == 3 ? (BRP_FFT_P1_LAYOUT == 1 ? 2 : 4) : PASS == 2 ? (L == 2048 ? (ROWS == 8 ? 2 : 4) : L == 1024 ? 4 : L == 512 ? 2 : (L == 4096 || L == 16) ? 0 : 1)
                                            : (L == 1024 ? 2 : ROWS == 4 ? (L % 3 == 0 ? 1 : 2) : ROWS == 2 ? (L == 4096 ? 8 : 4) : 1);
     // permute the low four bits of the butterfly index in the first (global -> shared) stage of pass 1
-    static constexpr bool ROT0 = PASS != 2 && L != 1024 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
+    // (the tensor-copy pass 1, PASS 3, needs none: with its pitch of 12 mod 16 plain row-fast lanes are conflict-free both in the dense
+    //  read and in the padded write of stage 0; the matching lane map of its last stage is in the kernel)
+    static constexpr bool ROT0 = (PASS == 1 || (PASS == 3 && BRP_FFT_P1_LAYOUT == 1)) && L != 1024 && (ROWS == 4 || ROWS == 8 || (ROWS == 2 && L != 4096));
     __host__ __device__ static constexpr int phys(int pos) { return pos + C4 * (pos >> 4) + C5 * (pos >> 5) + C8 * (pos >> 8); }
     static constexpr int PITCH = phys(L) + EXTRA;
     static constexpr int BYTES = ROWS * PITCH * 8;
@@ -436,7 +441,7 @@ fft_pass1_kernel(const float *__restrict__ in, size_t in_stride, const uint32_t 
 // DENSE in shared memory ([row][column]) without passing through the LSU, stage 0 reads it from there, and the last
 // stage puts its results back in the same dense form for eight tensor stores.  The dense image and the padded
 // exchange layout share the same shared memory, so stage 0 and the last stage read everything before anybody writes.
-// Lane mappings and padding chosen with tools/pass1_tma_layout.py (all accesses conflict-free except the dense read).
+// Lane mappings and padding chosen with tools/pass1_tma_layout.py: every shared-memory access of the kernel is conflict-free.
 // Arithmetic is the same as in fft_pass1_kernel (same butterflies, same twiddle construction): results are bit-identical.
 constexpr int kTmaL = 2048, kTmaRows = 4, kTmaBox = 256;
 #ifndef BRP_FFT_PASS2_TREE
@@ -556,8 +561,10 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     __syncthreads();
     tile_middle<L, ROWS, 3, 1, NS - 1>(tw, sm);
 
-    // last stage: radix 8 over consecutive positions.  Lanes take butterflies in transposed order (bf = 16 (x % 16) + x / 16)
-    // so that a half-warp produces consecutive k2 and its dense stores cover 128 contiguous bytes.
+    // last stage: radix 8 over consecutive positions.  Lanes take butterflies in transposed order (high nibble of the butterfly
+    // number = x % 16, so the four butterflies of a half-warp produce outputs k2 = 0..3 mod 4: the dense stores hit 16 different
+    // bank pairs) with the low nibble skewed by 2 t, t = (0, 1, 1, 2)[x % 4] (so that their padded READ positions differ mod 4 as
+    // well: with the row pitch of 12 mod 16 that makes the read conflict-free too).
     constexpr int PER = ROWS * (L / RL) / 512; // butterflies per thread (2)
     float2 v[PER][RL];
     int rows_[PER], kb_[PER];
@@ -565,7 +572,8 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     for (int it = 0; it < PER; ++it) {
         const int item = threadIdx.x + it * 512;
         const int row = item % ROWS, x = item / ROWS;
-        const int bf = 16 * (x % 16) + x / 16;
+        const int a4 = x & 3;
+        const int bf = BRP_FFT_P1_LAYOUT == 1 ? 16 * (x % 16) + x / 16 : 16 * (x % 16) + ((x / 16 + 2 * (a4 - (a4 >> 1))) & 15);
         const int base = bf * RL;
         rows_[it] = row;
         kb_[it] = freq_of_pos<L>(base);

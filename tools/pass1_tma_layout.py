@@ -40,10 +40,19 @@ def transpose16(x):  # 16 x 16 index transpose of an 8-bit butterfly number
     return 16 * (x % 16) + x // 16
 
 
+def skewed_transpose(x):
+    """like transpose16, with the low nibble of the butterfly number rotated by 2*t(a), t = (0, 1, 1, 2)[a % 4]: four consecutive
+    lanes then differ in (bf/2 + bf/32) mod 4 as well as in bf/16 mod 4, which is what a pitch of 4 (mod 16) needs in BOTH the padded
+    read and the dense write of the last stage"""
+    a, hi = x % 16, x // 16
+    return 16 * a + (hi + 2 * (0, 1, 1, 2)[a % 4]) % 16
+
+
 LANE_MAPS = {
     "row-fast": lambda item, BF: (item % ROWS, item // ROWS),
     "row-fast+rot": lambda item, BF: (item % ROWS, rot(item // ROWS)),
     "row-fast+T": lambda item, BF: (item % ROWS, transpose16(item // ROWS) if BF == 256 else item // ROWS),
+    "row-fast+T2": lambda item, BF: (item % ROWS, skewed_transpose(item // ROWS) if BF == 256 else item // ROWS),
     "bf-fast": lambda item, BF: (item // BF, item % BF),
 }
 
@@ -88,7 +97,7 @@ def main():
     for (name, phys), extra in itertools.product(rules.items(), range(0, 20)):
         pitch = phys(L) + extra
         padded = lambda row, base, j, S: row * pitch + phys(base + j * S)
-        for m0, m2 in itertools.product(("row-fast", "row-fast+rot"), ("row-fast", "row-fast+T")):
+        for m0, m2 in itertools.product(("row-fast", "row-fast+rot"), ("row-fast", "row-fast+T", "row-fast+T2")):
             c = {
                 "s0 dense LDS": stage_cost(0, m0, dense_in),
                 "s0 padded STS": stage_cost(0, m0, padded),
