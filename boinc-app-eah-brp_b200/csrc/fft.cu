@@ -245,8 +245,22 @@ enum { MAP_ROW_FAST = 0, MAP_BF_FAST = 1 };
 //     auto c = io.begin(row, base);   io.get(c, off);   io.put(c, off, q, value);
 // where base = blk*n + p is the butterfly's first position and off = j*S is a compile-time constant after
 // unrolling, so all per-element address arithmetic folds into immediates.
-template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, bool TREE = false, typename Load, typename Store>
-__device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store)
+// Who synchronises: the whole CTA (the default), or one group of cfg_threads(L) threads of a wider CTA that works on its own tile
+// (named barrier `id`; the persistent pass-1 kernel runs two such groups per CTA).
+struct CtaSync {
+    __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
+    __device__ __forceinline__ void sync() const { __syncthreads(); }
+};
+template <int NT>
+struct GroupSync {
+    int id, t;
+    __device__ __forceinline__ int tid() const { return t; }
+    __device__ __forceinline__ void sync() const { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(NT) : "memory"); }
+};
+
+template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, bool TREE = false, typename Load, typename Store,
+          typename Sync = CtaSync>
+__device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store, const Sync &sy = Sync())
 {
     constexpr int R = cfg_radix(L, STAGE);
     constexpr int n = cfg_n(L, STAGE);
@@ -259,7 +273,7 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
     static_assert(ITEMS % NT == 0, "tile must be a whole number of butterflies per thread");
 #pragma unroll
     for (int it = 0; it < ITEMS / NT; ++it) {
-        const int item = threadIdx.x + it * NT;
+        const int item = sy.tid() + it * NT;
         int row, bf;
         if (MAP == MAP_ROW_FAST) {
             row = item % ROWS;
@@ -278,7 +292,7 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
         for (int j = 0; j < R; ++j) v[j] = load.get(lc, j * S);
         if constexpr (SYNC_AFTER_LOAD) { // the store region overlaps the load region: everybody reads before anybody writes
             static_assert(ITEMS == NT, "one butterfly per thread");
-            __syncthreads();
+            sy.sync();
         }
         Dft<R>::run(v);
         const auto sc = store.begin(row, base);
@@ -325,14 +339,14 @@ struct SmemIO {
 };
 
 // middle stages (shared -> shared), recursively unrolled over the stage index
-template <int L, int ROWS, int PASS, int STAGE, int END>
-__device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm)
+template <int L, int ROWS, int PASS, int STAGE, int END, typename Sync = CtaSync>
+__device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm, const Sync &sy = Sync())
 {
     if constexpr (STAGE < END) {
         SmemIO<L, ROWS, PASS> io{sm};
-        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false>(tw, io, io); // (a power tree here is slower: measured 257 vs 250 us)
-        __syncthreads();
-        tile_middle<L, ROWS, PASS, STAGE + 1, END>(tw, sm);
+        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false>(tw, io, io, sy); // (a power tree here is slower: measured 257 vs 250 us)
+        sy.sync();
+        tile_middle<L, ROWS, PASS, STAGE + 1, END>(tw, sm, sy);
     }
 }
 
@@ -615,6 +629,148 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
         }
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+}
+
+
+// ------------------------------------------------------------------ pass 1, persistent (three tile buffers per SM)
+// In fft_pass1_tma_kernel a CTA loads its tile, waits for it (a fifth of all warp samples: profiles/README.md), transforms it
+// and leaves; two CTAs per SM cover each other's waits only in part, and a third does not fit the register file.  Here ONE
+// CTA of 1024 threads per SM stays for the whole launch and owns THREE tile buffers.  Its two halves of 512 threads work like
+// the two CTAs did -- same tile engine, same arithmetic, synchronising among themselves with named barriers -- on the tiles
+// n = 0, 1, 2, ... of the CTA in turn (even n: half 0, odd n: half 1; tile n lives in buffer n mod 3), and the tensor load of
+// tile n + 3 is issued into a buffer as soon as the stores of tile n have left it: a tile is under way for about half a tile time
+// before anybody waits for it.  Per buffer one mbarrier ("full"), completed by the tensor loads of each use in turn.  There is
+// no L2 prefetch here: the tensor load itself is the prefetch.
+#ifndef BRP_FFT_P1_PERSIST
+#define BRP_FFT_P1_PERSIST 1
+#endif
+
+template <int PARTS>
+__global__ void __launch_bounds__(1024, 1)
+fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
+                         const uint32_t *__restrict__ n_steps_arr, const float *__restrict__ mean_arr, uint32_t m1, uint32_t m,
+                         const float2 *__restrict__ tw, const float2 *__restrict__ tb, const float2 *__restrict__ tw_parts, uint32_t tiles_x,
+                         uint32_t total_tiles)
+{
+    constexpr int L = kTmaL, ROWS = kTmaRows, NS = cfg_stages(L), RL = cfg_radix(L, NS - 1);
+    constexpr int BUF = Layout<L, ROWS, 3>::BYTES; // 70 016 bytes: dense image and padded exchange layout share it
+    static_assert(BUF % 128 == 0, "tile buffers must keep the 128-byte alignment of tensor copies");
+    extern __shared__ __align__(128) unsigned char smraw[];
+    __shared__ __align__(8) unsigned long long full[3];
+    const int half = threadIdx.x >> 9, t = threadIdx.x & 511;
+    const GroupSync<512> sy{1 + half, t};
+    // tiles of this CTA: g(n) = blockIdx.x + n * gridDim.x  ->  (column tile bx, part, template b), bx fastest
+    const uint32_t my_tiles = total_tiles > blockIdx.x ? (total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
+    auto decode = [&](uint32_t n, uint32_t &bx, int &part, uint32_t &b) {
+        const uint32_t g = blockIdx.x + n * gridDim.x, rest = g / tiles_x;
+        bx = g - rest * tiles_x;
+        part = PARTS > 1 ? (int)(rest % PARTS) : -1;
+        b = PARTS > 1 ? rest / PARTS : rest;
+    };
+    // tensor load of tile n into buffer n % 3 (one thread)
+    auto issue_load = [&](uint32_t n) {
+        uint32_t bx, b;
+        int part;
+        decode(n, bx, part, b);
+        const uint32_t ns = n_steps_arr[b];
+        const uint32_t rows_needed = min((uint32_t)L, (ns + 2u * m1 - 1u) / (2u * m1));
+        const uint32_t boxes = (rows_needed + kTmaBox - 1) / kTmaBox;
+        const uint32_t bar_a = smem_addr(&full[n % 3]);
+        float2 *dst = reinterpret_cast<float2 *>(smraw + (size_t)(n % 3) * BUF);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(boxes * kTmaBox * ROWS * 8u) : "memory");
+        for (uint32_t k = 0; k < boxes; ++k)
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                             smem_addr(dst + k * kTmaBox * ROWS)),
+                         "l"(&in_map), "r"((int)(2u * bx * ROWS)), "r"((int)(k * kTmaBox)), "r"((int)b), "r"(bar_a)
+                         : "memory");
+    };
+    if (threadIdx.x == 0) {
+        for (int k = 0; k < 3; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&full[k])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (uint32_t n = 0; n < 3 && n < my_tiles; ++n) issue_load(n);
+    }
+    __syncthreads();
+
+    for (uint32_t n = (uint32_t)half; n < my_tiles; n += 2) {
+        uint32_t bx, b;
+        int part;
+        decode(n, bx, part, b);
+        float2 *sm = reinterpret_cast<float2 *>(smraw + (size_t)(n % 3) * BUF);
+        const uint32_t col0 = bx * ROWS;
+        const uint32_t n_steps = n_steps_arr[b];
+        const float mean = mean_arr[b];
+        {
+            const uint32_t bar_a = smem_addr(&full[n % 3]), parity = (n / 3) & 1u;
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                             : "=r"(done)
+                             : "r"(bar_a), "r"(parity)
+                             : "memory");
+        }
+        SmemIO<L, ROWS, 3> io{sm};
+        const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, part, PARTS, part > 0 ? tw_parts + (part - 1) * kTmaL : tw_parts};
+        tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true>(tw, dload, io, sy);
+        sy.sync();
+        tile_middle<L, ROWS, 3, 1, NS - 1>(tw, sm, sy);
+
+        constexpr int PER = ROWS * (L / RL) / 512;
+        float2 v[PER][RL];
+        int rows_[PER], kb_[PER];
+#pragma unroll
+        for (int it = 0; it < PER; ++it) {
+            const int item = t + it * 512;
+            const int row = item % ROWS, x = item / ROWS;
+            const int a4 = x & 3;
+            const int bf = BRP_FFT_P1_LAYOUT == 1 ? 16 * (x % 16) + x / 16 : 16 * (x % 16) + ((x / 16 + 2 * (a4 - (a4 >> 1))) & 15);
+            const int base = bf * RL;
+            rows_[it] = row;
+            kb_[it] = freq_of_pos<L>(base);
+            const float2 *c = io.begin(row, base);
+#pragma unroll
+            for (int j = 0; j < RL; ++j) v[it][j] = io.get(const_cast<float2 *>(c), j);
+        }
+        sy.sync(); // the dense image overwrites the padded tile
+        const float inv_m = 1.0f / (float)m;
+#pragma unroll
+        for (int it = 0; it < PER; ++it) {
+            Dft<RL>::run(v[it]);
+            const uint32_t col = col0 + rows_[it];
+            float sn, cs;
+            const uint32_t k2b = PARTS > 1 ? (uint32_t)PARTS * (uint32_t)kb_[it] + (uint32_t)part : (uint32_t)kb_[it];
+            sincospif(-2.0f * (float)(col * k2b) * inv_m, &sn, &cs);
+            const float2 a = make_float2(cs, sn);
+            const float2 *__restrict__ tq = tb + (size_t)col * RL;
+            float2 *d = sm + kb_[it] * ROWS + rows_[it];
+#pragma unroll
+            for (int q = 0; q < RL; ++q) {
+                const float2 w = (q == 0) ? a : cmul(a, __ldg(tq + q));
+                d[q * (L / RL) * ROWS] = cmul(v[it][out_slot<RL>(q)], w);
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        sy.sync();
+        if (t == 0) {
+#pragma unroll
+            for (int k = 0; k < L / kTmaBox; ++k) {
+                if constexpr (PARTS > 1)
+                    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%1, %2, %3, %4}], [%5];" ::"l"(&out_map),
+                                 "r"((int)(2u * col0)), "r"(part), "r"(k * kTmaBox), "r"((int)b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
+                                 : "memory");
+                else
+                    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&out_map),
+                                 "r"((int)(2u * col0)), "r"(k * kTmaBox), "r"((int)b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
+                                 : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            // Wait for the stores to have read the buffer and reload it AT ONCE: this thread's warp then enters its next tile a
+            // microsecond late, but the tile it loads -- the other half's next one -- gets its full half tile time of lead.
+            // (Measured: deferring the wait to after stage 0 of the next tile, when it costs nothing, makes the loads late:
+            // 558 us instead of 453 us per 64 templates.)
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            if (n + 3 < my_tiles) issue_load(n + 3);
+        }
     }
 }
 
@@ -1123,7 +1279,43 @@ static cudaError_t launch_fft(const BrpFftPlan &p, int mode, const float *in, si
     }
     const int tma_smem = Layout<kTmaL, kTmaRows, 3>::BYTES;
     const dim3 gp(p.m1 / kTmaRows, batch, parts > 0 ? parts : 1);
-    if (parts == 1)
+    // persistent form (one CTA of 1024 threads per SM, three tile buffers): BRP_FFT_PERSIST=0 selects the one-tile-per-CTA kernels
+    static const bool persist_off = BRP_FFT_P1_PERSIST == 0 || (getenv("BRP_FFT_PERSIST") && getenv("BRP_FFT_PERSIST")[0] == '0');
+    bool launched_persistent = false;
+    if (parts >= 1 && !persist_off) {
+        static int sms_on[64]; // resident CTAs = SMs, per device; 0 = not configured yet, -1 = not usable
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64) dev = 0;
+        const int psmem = 3 * tma_smem;
+        if (sms_on[dev] == 0) {
+            int sms = 0;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            const bool ok = sms > 0 &&
+                            cudaFuncSetAttribute((const void *)fft_pass1_persist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem) == cudaSuccess &&
+                            cudaFuncSetAttribute((const void *)fft_pass1_persist_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem) == cudaSuccess &&
+                            cudaFuncSetAttribute((const void *)fft_pass1_persist_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem) == cudaSuccess;
+            sms_on[dev] = ok ? sms : -1;
+            cudaGetLastError();
+        }
+        if (sms_on[dev] > 0) {
+            const uint32_t tiles_x = p.m1 / kTmaRows, total = tiles_x * (uint32_t)batch * (uint32_t)parts;
+            const uint32_t grid = total < (uint32_t)sms_on[dev] ? total : (uint32_t)sms_on[dev];
+            if (parts == 1)
+                fft_pass1_persist_kernel<1><<<grid, 1024, psmem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1, p.tw_inter_hi, nullptr,
+                                                                     tiles_x, total);
+            else if (parts == 2)
+                fft_pass1_persist_kernel<2><<<grid, 1024, psmem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_parts + 1 * kTmaL,
+                                                                     p.tw_inter_parts, p.tw_parts, tiles_x, total);
+            else
+                fft_pass1_persist_kernel<3><<<grid, 1024, psmem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_parts + 2 * kTmaL,
+                                                                     p.tw_inter_parts, p.tw_parts, tiles_x, total);
+            launched_persistent = true;
+        }
+    }
+    if (launched_persistent) {
+        // done above
+    } else if (parts == 1)
         fft_pass1_tma_kernel<1><<<gp, 512, tma_smem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_pass1, p.tw_inter_hi, nullptr);
     else if (parts == 2) // tw_parts: (parts-1) rows of W^{qp}, then the in-tile twiddles of the 2048-point stages
         fft_pass1_tma_kernel<2><<<gp, 512, tma_smem, st>>>(in_map, out_map, n_steps, mean, p.m1, p.m, p.tw_parts + 1 * kTmaL,
