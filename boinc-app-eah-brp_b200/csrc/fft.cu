@@ -647,6 +647,9 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
 #ifndef BRP_FFT_P1_PERSIST
 #define BRP_FFT_P1_PERSIST 1
 #endif
+#ifndef BRP_FFT_P1_BOXWISE
+#define BRP_FFT_P1_BOXWISE 1 // 0: reload a buffer only after ALL stores of the tile have read it (A/B runs)
+#endif
 
 template <int PARTS>
 __global__ void __launch_bounds__(1024, 1)
@@ -754,6 +757,7 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         sy.sync();
         if (t == 0) {
+            // one bulk group per box, so that each box of the buffer can be reloaded as soon as ITS store has read it
 #pragma unroll
             for (int k = 0; k < L / kTmaBox; ++k) {
                 if constexpr (PARTS > 1)
@@ -764,14 +768,32 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
                     asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&out_map),
                                  "r"((int)(2u * col0)), "r"(k * kTmaBox), "r"((int)b), "r"(smem_addr(sm + k * kTmaBox * ROWS))
                                  : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            // Wait for the stores to have read the buffer and reload it AT ONCE: this thread's warp then enters its next tile a
-            // microsecond late, but the tile it loads -- the other half's next one -- gets its full half tile time of lead.
-            // (Measured: deferring the wait to after stage 0 of the next tile, when it costs nothing, makes the loads late:
-            // 558 us instead of 453 us per 64 templates.)
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            if (n + 3 < my_tiles) issue_load(n + 3);
+            // Reload the buffer with tile n + 3 AT ONCE, box by box behind the stores: this thread's warp then enters its next tile
+            // a microsecond late, but the tile it loads -- the other half's next one -- gets its full lead.  (Measured: deferring
+            // the wait to a point of the next tile where it costs nothing makes the loads late: 515-558 us instead of 455 us per 64
+            // templates.)
+            uint32_t boxes3 = 0, bx3 = 0, b3 = 0;
+            if (n + 3 < my_tiles) {
+                int part3;
+                decode(n + 3, bx3, part3, b3);
+                const uint32_t need3 = min((uint32_t)L, (n_steps_arr[b3] + 2u * m1 - 1u) / (2u * m1));
+                boxes3 = (need3 + kTmaBox - 1) / kTmaBox;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&full[n % 3])), "r"(boxes3 * kTmaBox * ROWS * 8u)
+                             : "memory");
+            }
+            static_assert(L / kTmaBox == 8, "eight boxes per tile");
+#define BRP_RELOAD_BOX(k)                                                                                                               \
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(BRP_FFT_P1_BOXWISE ? 7 - (k) : 0) : "memory"); /* store k has read its box */ \
+    if ((uint32_t)(k) < boxes3)                                                                                                         \
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"( \
+                         smem_addr(sm + (k) * kTmaBox * ROWS)),                                                                         \
+                     "l"(&in_map), "r"((int)(2u * bx3 * ROWS)), "r"((int)((k) * kTmaBox)), "r"((int)b3), "r"(smem_addr(&full[n % 3]))    \
+                     : "memory");
+            BRP_RELOAD_BOX(0) BRP_RELOAD_BOX(1) BRP_RELOAD_BOX(2) BRP_RELOAD_BOX(3)
+            BRP_RELOAD_BOX(4) BRP_RELOAD_BOX(5) BRP_RELOAD_BOX(6) BRP_RELOAD_BOX(7)
+#undef BRP_RELOAD_BOX
         }
     }
 }
