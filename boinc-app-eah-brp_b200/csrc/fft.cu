@@ -1098,6 +1098,21 @@ int brp_fft_plan_create(BrpFftPlan *p, uint32_t n, uint32_t nu_hint)
         m1 = 1024;
         m2 = 4096;
     }
+    // shorter series (n = 2^20, 2^21 and three times that): a 2048-row pass 1 here too, so that it runs on the persistent
+    // tensor-copy kernel, and a shorter pass 2 (measured at 2^20: pass 1 117 instead of 153 us per 64 templates, pass 2 unchanged;
+    // whole search 180 k instead of 162 k templates/s; 2^21: 96.8 k instead of 86.1 k).  With the factor 3 the 6144 rows run as
+    // three 2048-row parts, which needs all samples inside the first 2048 rows.
+    if ((a == 19 || a == 20) && (odd == 1 || (nu_hint != 0 && nu_hint <= 2u * (m / 6144u) * 2048u))) {
+        m2 = 2048u * odd;
+        m1 = m / m2;
+    }
+    if (const char *force = getenv("BRP_FFT_M2")) { // measurement aid: another split of the same length
+        const uint32_t f = (uint32_t)atoi(force);
+        if (f >= 16 && m % f == 0 && find_tile(f) && find_tile(m / f)) {
+            m2 = f;
+            m1 = m / f;
+        }
+    }
     const TileInfo *t1 = find_tile(m2), *t2 = find_tile(m1);
     if (!t1 || !t2) return RADPUL_CUDA_FFT_PLAN;
     p->n = n; p->m = m; p->m1 = m1; p->m2 = m2; p->radix3 = (odd == 3);
