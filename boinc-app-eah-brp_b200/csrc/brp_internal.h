@@ -37,7 +37,8 @@ cudaError_t brp_launch_count_mismatch(const int32_t *a, const int32_t *b, uint32
 cudaError_t brp_launch_resample(const float *series, const BrpTemplateDev *tmpl, int batch, const BrpGeomDev &g,
                                 float *out, size_t out_stride, int32_t *idx_out, uint32_t *n_steps, float *mean,
                                 double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st,
-                                bool every_sample = false /* skip the run detection: timing model at every sample */);
+                                bool every_sample = false /* skip the run detection: timing model at every sample */,
+                                const BrpTemplateDev *tmpl_value = nullptr /* tmpl == NULL, batch 1: the template itself (host memory) */);
 cudaError_t brp_launch_sin_lut(const float *x, float *out, uint32_t n, cudaStream_t st);
 cudaError_t brp_launch_round_index(const float *f, int32_t *out, uint32_t n, cudaStream_t st);
 
@@ -100,8 +101,12 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
 cudaError_t brp_launch_collect(const unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits,
                                uint32_t max_hits, uint32_t *counter, cudaStream_t st);
 
-// the same, and every non-empty entry is zeroed behind the scan (the table is empty again afterwards)
-cudaError_t brp_launch_collect_and_clear(unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits, uint32_t max_hits,
-                                         uint32_t *counter, cudaStream_t st);
+// One-template-per-call callers (the reference's backend interface): the same scan, but every non-empty entry is zeroed behind
+// it (the table is empty again afterwards) and the hits go STRAIGHT to the caller's mapped pinned host memory, `hits` being its
+// device-side address, with their number in *host_count (mapped pinned as well) -- no device-to-host copy to enqueue and await.
+// ctl: three device words, all zero before the first call: slot counters of even and odd calls (`which` = 0 / 1; each call zeroes the
+// other one for the next call, which therefore needs no memset) and the arrival count of the blocks.
+cudaError_t brp_launch_collect_to_host(unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits, uint32_t max_hits,
+                                       uint32_t *ctl, int which, uint32_t *host_count, cudaStream_t st);
 
 #endif

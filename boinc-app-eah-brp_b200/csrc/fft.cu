@@ -1272,8 +1272,10 @@ static int pass1_tma_maps(const BrpFftPlan &p, const float *in, size_t in_stride
 // m2 * ceil(count / m2) floats per template (out_stride says how many it holds).
 static bool pass2_tma_map(const BrpFftPlan &p, const float *out, size_t out_stride, uint32_t count, int batch, CUtensorMap *map)
 {
-    if (p.m1 != 1024 || p.m2 < 16 || count == 0 || count > p.m) return false;
-    const uint32_t rows = (count + p.m2 - 1) / p.m2;
+    // (count = m + 1, the whole spectrum with its Nyquist bin as the reference's run_fft wants it: bin m is the mirror of bin 0 and
+    //  is written by the edge tile's own stores, all m1 rows go through the map)
+    if (p.m1 != 1024 || p.m2 < 16 || count == 0 || count > p.m + 1) return false;
+    const uint32_t rows = ((count < p.m ? count : p.m) + p.m2 - 1) / p.m2;
     if ((size_t)rows * p.m2 > out_stride || (out_stride & 3) || ((uintptr_t)out & 15)) return false;
     tensor_map_encode_fn enc = tensor_map_encoder();
     if (!enc) return false;

@@ -254,15 +254,18 @@ harmonic_summing_kernel(const float *__restrict__ ps, size_t ps_stride, BrpGeomD
 #undef BRP_HS_STEP
 }
 
-// clear: leave the table empty behind the scan (one-template-per-call callers: saves them a memset of the whole table per call)
+// TO_HOST (one-template-per-call callers): the table is left empty behind the scan (saves a memset of the whole table per call),
+// `hits` is mapped host memory, and the block that finishes last publishes the hit count there and resets the control words
+template <bool TO_HOST>
 __global__ void collect_kernel(unsigned long long *__restrict__ keys, uint32_t fu, uint32_t w2,
-                               brp_hit *__restrict__ hits, uint32_t max_hits, uint32_t *__restrict__ counter, bool clear)
+                               brp_hit *__restrict__ hits, uint32_t max_hits, uint32_t *__restrict__ counter,
+                               uint32_t *__restrict__ next_counter, uint32_t *__restrict__ arrived, uint32_t *__restrict__ host_count)
 {
     const uint32_t total = 5u * fu;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
         const unsigned long long key = keys[e];
         if (key == 0ull) continue;
-        if (clear) keys[e] = 0ull;
+        if (TO_HOST) keys[e] = 0ull;
         const uint32_t k = e / fu, bin = e - k * fu;
         if (bin < w2) continue; // the candidate scan starts at window_2 (demod_binary.c:1323)
         const uint32_t slot = atomicAdd(counter, 1u);
@@ -273,6 +276,19 @@ __global__ void collect_kernel(unsigned long long *__restrict__ keys, uint32_t f
             h.tmpl = 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull);
             h.harm_idx = k;
             hits[slot] = h;
+        }
+    }
+    if constexpr (TO_HOST) {
+        __syncthreads(); // this block's slot requests are all issued
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(arrived, 1u) == gridDim.x - 1) {
+                __threadfence();
+                const uint32_t n = atomicAdd(counter, 0u);
+                *host_count = n < max_hits ? n : max_hits;
+                *next_counter = 0u;
+                *arrived = 0u;
+            }
         }
     }
 }
@@ -311,13 +327,13 @@ cudaError_t brp_launch_harmonic_summing(const float *ps, size_t ps_stride, int b
 cudaError_t brp_launch_collect(const unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits,
                                uint32_t max_hits, uint32_t *counter, cudaStream_t st)
 {
-    collect_kernel<<<296, 256, 0, st>>>(const_cast<unsigned long long *>(keys), fu, w2, hits, max_hits, counter, false);
+    collect_kernel<false><<<296, 256, 0, st>>>(const_cast<unsigned long long *>(keys), fu, w2, hits, max_hits, counter, nullptr, nullptr, nullptr);
     return cudaGetLastError();
 }
 
-cudaError_t brp_launch_collect_and_clear(unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits, uint32_t max_hits,
-                                         uint32_t *counter, cudaStream_t st)
+cudaError_t brp_launch_collect_to_host(unsigned long long *keys, uint32_t fu, uint32_t w2, brp_hit *hits, uint32_t max_hits,
+                                       uint32_t *ctl, int which, uint32_t *host_count, cudaStream_t st)
 {
-    collect_kernel<<<296, 256, 0, st>>>(keys, fu, w2, hits, max_hits, counter, true);
+    collect_kernel<true><<<296, 256, 0, st>>>(keys, fu, w2, hits, max_hits, ctl + (which & 1), ctl + ((which & 1) ^ 1), ctl + 2, host_count);
     return cudaGetLastError();
 }

@@ -31,7 +31,6 @@ struct LegacyState {
     // resampling
     BrpGeomDev gd;
     float *d_series, *d_resamp;
-    BrpTemplateDev *d_tmpl;
     uint32_t *d_nsteps;
     float *d_mean;
     double *d_partials;
@@ -45,9 +44,11 @@ struct LegacyState {
     float *d_mean_zero;
     // harmonic summing
     unsigned long long *d_keys;
-    // device: [counter (one brp_hit-sized slot)][hits ...], so that the counter and the first kLegacyFirstHits hits come back
-    // in ONE copy; host mirror in pinned memory
+    // mapped pinned host memory the collecting kernel writes straight into: [hit count (one brp_hit-sized slot)][hits ...];
+    // d_hitbuf is the same memory as the device sees it.  d_ctl: the kernel's three control words (brp_launch_collect_to_host)
     brp_hit *d_hitbuf, *h_hitbuf;
+    uint32_t *d_ctl;
+    unsigned calls; // parity of the control words
     uint32_t hit_cap;
     float *h_spectrum; // handed out as sumspec[0]: the spectrum's values above threshold, 0 elsewhere
     uint32_t fu, ps_stride;
@@ -67,8 +68,6 @@ LegacyState L;
     } while (0)
 
 inline float *as_dev(DIfloatPtr p) { return reinterpret_cast<float *>(p.device_ptr); }
-
-constexpr uint32_t kLegacyFirstHits = 255; // with the counter slot: one 4 KB transfer covers nearly every template
 
 } // namespace
 
@@ -122,7 +121,6 @@ int set_up_resampling(DIfloatPtr input, DIfloatPtr *output, const RESAMP_PARAMS 
     const size_t nu4 = ((size_t)nu + 3) & ~(size_t)3, n4 = ((size_t)n + 3) & ~(size_t)3;
     LG_TRY(cudaMalloc((void **)&L.d_series, sizeof(float) * nu4), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_resamp, sizeof(float) * n4), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMalloc((void **)&L.d_tmpl, sizeof(BrpTemplateDev)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_nsteps, sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_mean, sizeof(float)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
     LG_TRY(cudaMalloc((void **)&L.d_partials, sizeof(double) * brp_resamp_blocks(nu)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
@@ -143,10 +141,10 @@ int run_resampling(DIfloatPtr input, DIfloatPtr output, const RESAMP_PARAMS *par
     g.dt = params->dt;
     g.step_inv = params->step_inv;
     const BrpTemplateDev t = {params->tau, params->Omega, params->Psi0, params->S0};
-    LG_TRY(cudaMemcpyAsync(L.d_tmpl, &t, sizeof(t), cudaMemcpyHostToDevice, L.stream), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     const size_t n4 = ((size_t)g.n + 3) & ~(size_t)3;
-    LG_TRY(brp_launch_resample(L.d_series, L.d_tmpl, 1, g, L.d_resamp, n4, NULL, L.d_nsteps, L.d_mean, L.d_partials, L.d_counters,
-                               false, L.stream),
+    // the template travels as a kernel argument: nothing to upload first
+    LG_TRY(brp_launch_resample(L.d_series, NULL, 1, g, L.d_resamp, n4, NULL, L.d_nsteps, L.d_mean, L.d_partials, L.d_counters,
+                               false, L.stream, false, &t),
            RADPUL_CUDA_KERNEL_INVOKE);
     L.resampled = true;
     return 0;
@@ -157,9 +155,9 @@ int tear_down_resampling(DIfloatPtr output)
     (void)output;
     if (!L.initialised) return 0;
     cudaSetDevice(L.device);
-    cudaFree(L.d_series); cudaFree(L.d_resamp); cudaFree(L.d_tmpl); cudaFree(L.d_nsteps); cudaFree(L.d_mean);
+    cudaFree(L.d_series); cudaFree(L.d_resamp); cudaFree(L.d_nsteps); cudaFree(L.d_mean);
     cudaFree(L.d_partials); cudaFree(L.d_counters);
-    L.d_series = L.d_resamp = NULL; L.d_tmpl = NULL; L.d_nsteps = NULL; L.d_mean = NULL; L.d_partials = NULL; L.d_counters = NULL;
+    L.d_series = L.d_resamp = NULL; L.d_nsteps = NULL; L.d_mean = NULL; L.d_partials = NULL; L.d_counters = NULL;
     return 0;
 }
 
@@ -240,8 +238,12 @@ int set_up_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int *nr_p
     L.fu = fundamental_idx_hi;
     L.hit_cap = 5u * (fundamental_idx_hi ? fundamental_idx_hi : 1u);
     LG_TRY(cudaMalloc((void **)&L.d_keys, sizeof(unsigned long long) * L.hit_cap), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMalloc((void **)&L.d_hitbuf, sizeof(brp_hit) * ((size_t)L.hit_cap + 1)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
-    LG_TRY(cudaMallocHost((void **)&L.h_hitbuf, sizeof(brp_hit) * ((size_t)L.hit_cap + 1)), RADPUL_CUDA_MEM_ALLOC_HOST);
+    LG_TRY(cudaHostAlloc((void **)&L.h_hitbuf, sizeof(brp_hit) * ((size_t)L.hit_cap + 1), cudaHostAllocMapped), RADPUL_CUDA_MEM_ALLOC_HOST);
+    LG_TRY(cudaHostGetDevicePointer((void **)&L.d_hitbuf, L.h_hitbuf, 0), RADPUL_CUDA_MEM_ALLOC_HOST);
+    memset(L.h_hitbuf, 0, sizeof(brp_hit));
+    LG_TRY(cudaMalloc((void **)&L.d_ctl, 4 * sizeof(uint32_t)), RADPUL_CUDA_MEM_ALLOC_DEVICE);
+    LG_TRY(cudaMemset(L.d_ctl, 0, 4 * sizeof(uint32_t)), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
+    L.calls = 0;
     // the per-bin table starts empty and is left empty by every run_harmonic_summing (the collecting kernel clears what it reads)
     LG_TRY(cudaMemset(L.d_keys, 0, sizeof(unsigned long long) * L.hit_cap), RADPUL_CUDA_MEM_COPY_HOST_DEVICE);
     L.h_spectrum = (float *)calloc(fundamental_idx_hi ? fundamental_idx_hi : 1, sizeof(float));
@@ -273,20 +275,13 @@ int run_harmonic_summing(float **sumspec, int32_t **dirty, unsigned int nr_pages
     g.h = harmonic_idx_hi;
     BrpThresholds t;
     for (int k = 0; k < 5; k++) t.t[k] = thresholds[k];
-    uint32_t *const d_counter = reinterpret_cast<uint32_t *>(L.d_hitbuf);
-    LG_TRY(cudaMemsetAsync(d_counter, 0, sizeof(uint32_t), L.stream), RADPUL_CUDA_KERNEL_INVOKE);
+    // three launches and no copy per template: the collecting kernel writes the hits and their number into mapped host memory
     LG_TRY(brp_launch_harmonic_summing(as_dev(powerspectrum), L.ps_stride, 1, g, t, 0, L.d_keys, L.stream), RADPUL_CUDA_KERNEL_INVOKE);
-    LG_TRY(brp_launch_collect_and_clear(L.d_keys, fundamental_idx_hi, 0, L.d_hitbuf + 1, L.hit_cap, d_counter, L.stream),
+    LG_TRY(brp_launch_collect_to_host(L.d_keys, fundamental_idx_hi, 0, L.d_hitbuf + 1, L.hit_cap, L.d_ctl, (int)(L.calls++ & 1u),
+                                      reinterpret_cast<uint32_t *>(L.d_hitbuf), L.stream),
            RADPUL_CUDA_KERNEL_INVOKE);
-    LG_TRY(cudaMemcpyAsync(L.h_hitbuf, L.d_hitbuf, sizeof(brp_hit) * (1 + kLegacyFirstHits), cudaMemcpyDeviceToHost, L.stream),
-           RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
     LG_TRY(cudaStreamSynchronize(L.stream), RADPUL_CUDA_KERNEL_INVOKE); // the one synchronisation of a template
-    const uint32_t n = *reinterpret_cast<const uint32_t *>(L.h_hitbuf);
-    if (n > kLegacyFirstHits) { // rare: more hits than the first transfer holds
-        LG_TRY(cudaMemcpy(L.h_hitbuf + 1 + kLegacyFirstHits, L.d_hitbuf + 1 + kLegacyFirstHits, sizeof(brp_hit) * (n - kLegacyFirstHits),
-                          cudaMemcpyDeviceToHost),
-               RADPUL_CUDA_MEM_COPY_DEVICE_HOST);
-    }
+    const uint32_t n = *reinterpret_cast<const volatile uint32_t *>(L.h_hitbuf);
     for (uint32_t i = 0; i < n; i++) {
         const brp_hit &h = L.h_hitbuf[1 + i];
         sumspec[h.harm_idx][h.bin] = h.power; // harm_idx 0: the spectrum bin itself (P[i] > thr[0], hs_common.c:79)
@@ -305,8 +300,8 @@ int tear_down_harmonic_summing(float **sumspec, int32_t **dirty)
         for (int i = 0; i < 5; i++) { free(dirty[i]); dirty[i] = NULL; }
     if (!L.initialised) return 0;
     cudaSetDevice(L.device);
-    cudaFree(L.d_keys); cudaFree(L.d_hitbuf); cudaFreeHost(L.h_hitbuf); free(L.h_spectrum);
-    L.d_keys = NULL; L.d_hitbuf = NULL; L.h_hitbuf = NULL; L.h_spectrum = NULL;
+    cudaFree(L.d_keys); cudaFree(L.d_ctl); cudaFreeHost(L.h_hitbuf); free(L.h_spectrum);
+    L.d_keys = NULL; L.d_ctl = NULL; L.d_hitbuf = NULL; L.h_hitbuf = NULL; L.h_spectrum = NULL;
     return 0;
 }
 

@@ -65,8 +65,9 @@ constexpr int kGroups = BRP_RESAMP_THREADS;                                    /
 static_assert(kGroupLen == 16 && 128 % kGroupLen == 0, "the lane mapping below assumes 16-sample groups");
 // A block walks kChunks chunks: the block-level epilogue (reduction, fence, atomic) is a serial chain of a few
 // microseconds, and with one chunk per block that chain, not bandwidth or issue slots, set the kernel's duration.
-constexpr int kChunks = 4;
-constexpr uint32_t kBlockSpan = (uint32_t)kChunks * BRP_RESAMP_SAMPLES_PER_BLOCK; // 8 warps x kChunks segments of 512
+// (One or two templates per launch -- the reference's one-template-at-a-time interface -- are the exception: 256 blocks
+// per template leave most of the 148 SMs' slots empty, so those launches run with one chunk per block.)
+constexpr int kChunksBatched = 4;
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -80,14 +81,15 @@ __device__ __forceinline__ double warp_sum(double v)
 #ifndef BRP_RESAMP_MIN_BLOCKS
 #define BRP_RESAMP_MIN_BLOCKS 8
 #endif
-template <int MODE, bool WRITE_IDX>
+template <int MODE, bool WRITE_IDX, int kChunks = kChunksBatched>
 __global__ void __launch_bounds__(BRP_RESAMP_THREADS, BRP_RESAMP_MIN_BLOCKS)
 resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restrict__ tmpl, BrpGeomDev g,
                 float *__restrict__ out, size_t out_stride, int32_t *__restrict__ idx_out,
                 uint32_t *__restrict__ n_steps_out, float *__restrict__ mean_out, double *__restrict__ partials,
-                uint32_t *__restrict__ counters)
+                uint32_t *__restrict__ counters, const BrpTemplateDev tmpl_value)
 {
     constexpr bool FAST = MODE != 0;
+    constexpr uint32_t kBlockSpan = (uint32_t)kChunks * BRP_RESAMP_SAMPLES_PER_BLOCK; // 8 warps x kChunks segments of 512
     __shared__ float2 s_tab[65];
     __shared__ int s_nsteps;
     __shared__ double s_warp[BRP_RESAMP_THREADS / 32];
@@ -96,7 +98,7 @@ resample_kernel(const float *__restrict__ series, const BrpTemplateDev *__restri
     const int b = blockIdx.y;
     const uint32_t nblk = gridDim.x;
     const uint32_t block_lo = blockIdx.x * kBlockSpan;
-    const BrpTemplateDev tp = tmpl[b];
+    const BrpTemplateDev tp = tmpl ? tmpl[b] : tmpl_value; // one template handed over as a kernel argument: no upload before the launch
     const uint32_t nu = g.nu;
 
     if (threadIdx.x < 65) s_tab[threadIdx.x] = c_brp_sincos[threadIdx.x];
@@ -367,26 +369,33 @@ cudaError_t brp_launch_count_mismatch(const int32_t *a, const int32_t *b, uint32
 
 cudaError_t brp_launch_resample(const float *series, const BrpTemplateDev *tmpl, int batch, const BrpGeomDev &g,
                                 float *out, size_t out_stride, int32_t *idx_out, uint32_t *n_steps, float *mean,
-                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st, bool every_sample)
+                                double *partials, uint32_t *counters, bool fill_padding, cudaStream_t st, bool every_sample,
+                                const BrpTemplateDev *tmpl_value)
 {
+    if (!tmpl && (!tmpl_value || batch != 1)) return cudaErrorInvalidValue;
+    const BrpTemplateDev tv = tmpl_value ? *tmpl_value : BrpTemplateDev{};
+    constexpr uint32_t kBlockSpan = (uint32_t)kChunksBatched * BRP_RESAMP_SAMPLES_PER_BLOCK;
     const dim3 grid((g.nu + kBlockSpan - 1) / kBlockSpan, batch);
     // the FP32 index path needs every i - del_t below 2^23; |del_t| is far below 2^22 for any sane template
     const bool fast = g.nu <= (1u << 22);
-    if (fast && !every_sample) {
+    if (fast && !every_sample && !idx_out && batch <= 2) {
+        const dim3 fine(brp_resamp_blocks(g.nu), batch);
+        resample_kernel<2, false, 1><<<fine, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
+    } else if (fast && !every_sample) {
         if (idx_out)
-            resample_kernel<2, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<2, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
         else
-            resample_kernel<2, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<2, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
     } else if (fast) {
         if (idx_out)
-            resample_kernel<1, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<1, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
         else
-            resample_kernel<1, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<1, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
     } else {
         if (idx_out)
-            resample_kernel<0, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<0, true><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
         else
-            resample_kernel<0, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters);
+            resample_kernel<0, false><<<grid, BRP_RESAMP_THREADS, 0, st>>>(series, tmpl, g, out, out_stride, idx_out, n_steps, mean, partials, counters, tv);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
