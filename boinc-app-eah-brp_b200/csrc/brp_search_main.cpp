@@ -13,6 +13,12 @@
 // template indices make "earliest template" well defined.  No NCCL here: inside one process there is nothing to
 // exchange between the devices themselves.
 //
+// Several work-units in one invocation (-i a -o a.cand -i b -o b.cand ...): the passes of the reference's BOINC wrapper
+// (erp_boinc_wrapper.cpp:430-474) -- each input is searched into the output of the same position, a pass whose output file
+// exists already is skipped, and the checkpoint file is deleted after every completed pass so that the next one does not pick
+// it up.  With --devices the passes are dealt out over the devices, one work-unit per device at a time (short work-units do not
+// need more than one GPU each, and nothing is exchanged at all); each pass then keeps its own checkpoint file "<name>.<pass>".
+//
 // There is no CPU path in here: every stage of the search runs in the CUDA kernels of the library, and the program
 // fails with the library's RADPUL_* code when no device is usable.
 #include <stdio.h>
@@ -21,6 +27,7 @@
 #include <time.h>
 
 #include <algorithm>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -30,6 +37,7 @@ namespace {
 
 struct Options {
     const char *input = nullptr, *output = nullptr, *bank = nullptr, *checkpoint = nullptr, *zaplist = nullptr;
+    std::vector<const char *> inputs, outputs; /* every -i / -o given, in order: the passes */
     int white = 0, device = 0, debug = 0;
     float f0 = 250.0f, padding = 1.0f, fA = 0.04f; /* defaults of demod_binary.c:204-215 */
     unsigned window = 1000;
@@ -66,8 +74,8 @@ bool parse_devices(const char *v, std::vector<int> &out)
 void usage(const char *argv0)
 {
     printf("Usage: %s [options]\n"
-           " -i, --input_file       string  work-unit (.bin4 or .binary, zlib or plain)\n"
-           " -o, --output_file      string  candidate file\n"
+           " -i, --input_file       string  work-unit (.bin4 or .binary, zlib or plain); may be repeated, with as many -o\n"
+           " -o, --output_file      string  candidate file (a pass whose output exists already is skipped when there are several)\n"
            " -t, --template_bank    string  template bank (P tau Psi0 per line)\n"
            " -c, --checkpoint_file  string  checkpoint file (read on start if present)\n"
            " -l, --zaplist_file     string  zap list: \"fmin fmax\" in Hz per line (required with -W)\n"
@@ -78,6 +86,7 @@ void usage(const char *argv0)
            " -B, --box              int     running-median window (default 1000)\n"
            " -D, --device           int     CUDA device (default 0)\n"
            "     --devices          list    several GPUs of this box, e.g. 0-7 or 0,2,4: the bank is split over them\n"
+           "                                (several work-units: one work-unit per device at a time instead)\n"
            " -z, --debug                    more output\n"
            "     --chunk            int     templates per enqueue between checkpoint opportunities (default 2048)\n"
            "     --batch            int     templates per kernel launch (default 64)\n"
@@ -131,7 +140,11 @@ int parse(int argc, char **argv, Options &o)
                 return RADPUL_EFILE;
             }
             o.input = v;
-        } else if (is(a, "-o", "--output_file")) o.output = v;
+            o.inputs.push_back(v);
+        } else if (is(a, "-o", "--output_file")) {
+            o.output = v;
+            o.outputs.push_back(v);
+        }
         else if (is(a, "-c", "--checkpoint_file")) o.checkpoint = v;
         else if (is(a, "-t", "--template_bank")) o.bank = v;
         else if (is(a, "-l", "--zaplist_file")) o.zaplist = v;
@@ -161,6 +174,10 @@ int parse(int argc, char **argv, Options &o)
         fprintf(stderr, "Input file, output file and template bank are required.\n");
         return RADPUL_EMISC;
     }
+    if (o.inputs.size() != o.outputs.size()) { /* erp_boinc_wrapper.cpp:412-416 */
+        fprintf(stderr, "Number of input files (%zu) and output files (%zu) differ.\n", o.inputs.size(), o.outputs.size());
+        return RADPUL_EMISC;
+    }
     return 0;
 }
 
@@ -182,12 +199,9 @@ double now_s()
         }                                                                        \
     } while (0)
 
-int main(int argc, char **argv)
+/* one work-unit: o.input -> o.output on o.devices (the whole of demod_binary.c MAIN behind the option parsing) */
+static int run_pass(Options o)
 {
-    Options o;
-    int rc = parse(argc, argv, o);
-    if (rc) return rc;
-
     /* ---- resume: demod_binary.c:560-652 ---- */
     uint32_t done = 0;
     bool resumed = false;
@@ -336,5 +350,65 @@ int main(int argc, char **argv)
     CHECK(brp_write_candidates(o.output, merged.data(), &g, tsample_us));
     for (brp_search *h : handles) CHECK(brp_search_destroy(h));
     brp_bank_free(bank);
+    return 0;
+}
+
+int main(int argc, char **argv)
+{
+    Options o;
+    int rc = parse(argc, argv, o);
+    if (rc) return rc;
+    const size_t passes = o.inputs.size();
+    if (passes == 1) return run_pass(o);
+
+    /* ---- several work-units: the wrapper's passes (erp_boinc_wrapper.cpp:430-474) ---- */
+    if (o.devices.empty()) o.devices.push_back(o.device);
+    const size_t ndev = std::min(o.devices.size(), passes);
+    std::vector<int> rcs(passes, 0);
+    std::vector<std::string> cp_names(passes);
+    auto one = [&](size_t pass, int device) {
+        Options po = o;
+        po.input = o.inputs[pass];
+        po.output = o.outputs[pass];
+        po.device = device;
+        po.devices.assign(1, device);
+        if (o.checkpoint) {
+            /* sequential passes share the one checkpoint file like the wrapper's; concurrent ones need one each */
+            cp_names[pass] = ndev > 1 ? std::string(o.checkpoint) + "." + std::to_string(pass) : std::string(o.checkpoint);
+            po.checkpoint = cp_names[pass].c_str();
+        }
+        if (FILE *fp = fopen(po.output, "r")) { /* :452-456 */
+            fclose(fp);
+            fprintf(stderr, "Output file: '%s' already exists - skipping pass\n", po.output);
+            return;
+        }
+        rcs[pass] = run_pass(po);
+        if (rcs[pass]) {
+            fprintf(stderr, "Demodulation failed (error: %i)!\n", rcs[pass]);
+            return;
+        }
+        /* a pass that stopped early (--max_templates) has no output yet and keeps its checkpoint */
+        FILE *done = fopen(po.output, "r");
+        if (done) fclose(done);
+        if (done && po.checkpoint) remove(po.checkpoint); /* :466-467 */
+    };
+    if (ndev == 1) {
+        for (size_t pass = 0; pass < passes; pass++) {
+            one(pass, o.devices[0]);
+            if (rcs[pass]) return rcs[pass]; /* the wrapper stops at the first failing pass */
+        }
+        return 0;
+    }
+    std::vector<std::thread> workers;
+    for (size_t d = 0; d < ndev; d++)
+        workers.emplace_back([&, d]() {
+            for (size_t pass = d; pass < passes; pass += ndev) {
+                one(pass, o.devices[d]);
+                if (rcs[pass]) return;
+            }
+        });
+    for (std::thread &w : workers) w.join();
+    for (size_t pass = 0; pass < passes; pass++)
+        if (rcs[pass]) return rcs[pass];
     return 0;
 }

@@ -112,6 +112,51 @@ def test_cli_bank_split_over_several_devices_gives_the_same_file(wu):
     assert r.returncode == brp_b200.RADPUL_EVAL
 
 
+def test_cli_several_work_units_in_one_invocation(wu):
+    """The passes of the reference's BOINC wrapper (erp_boinc_wrapper.cpp:430-474): -i/-o pairs are searched in turn, a pass
+    whose output exists is skipped, the checkpoint file is removed after each completed pass; with --devices the work-units
+    are dealt out over the devices (one each at a time, own checkpoint files) and give the same bytes."""
+    rng = np.random.default_rng(5)
+    base = np.frombuffer((wu / "wu.binary").read_bytes(), np.uint8)
+    names = ["wu.binary"]
+    for k in (1, 2):                                # two more work-units: the same header, other noise in the samples
+        other = base.copy()
+        samples = other[1168:].view(np.int8).astype(np.int16) + rng.integers(-3, 4, len(other) - 1168)
+        other[1168:] = np.clip(samples, -128, 127).astype(np.int8).view(np.uint8)
+        names.append(f"wu{k}.binary")
+        (wu / names[-1]).write_bytes(other.tobytes())
+    common = ["-t", str(wu / "bank.txt"), "-f", "400", "-A", "0.08", "-P", "1.0", "-B", "200", "-z"]
+    for k, name in enumerate(names):                # one invocation each: the expected files
+        r = subprocess.run([str(EXE), "-i", str(wu / name), "-o", str(wu / f"single{k}.cand")] + common, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+    assert (wu / "single0.cand").read_bytes() != (wu / "single1.cand").read_bytes()
+
+    def pairs(prefix):
+        out = []
+        for k, name in enumerate(names):
+            out += ["-i", str(wu / name), "-o", str(wu / f"{prefix}{k}.cand")]
+        return out
+
+    (wu / "seq1.cand").write_text("already there\n")                                   # pass 1 must be skipped
+    r = subprocess.run([str(EXE)] + pairs("seq") + common + ["-c", str(wu / "seq.cpt")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "seq1.cand' already exists - skipping pass" in r.stderr
+    assert (wu / "seq1.cand").read_text() == "already there\n"
+    for k in (0, 2):
+        assert (wu / f"seq{k}.cand").read_bytes() == (wu / f"single{k}.cand").read_bytes()
+    assert not (wu / "seq.cpt").exists()                                               # removed after the last pass too
+    import torch
+    n = torch.cuda.device_count()
+    r = subprocess.run([str(EXE)] + pairs("par") + common + ["-c", str(wu / "par.cpt"), "--devices", f"0-{n - 1}" if n > 1 else "0,0"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    for k in range(3):
+        assert (wu / f"par{k}.cand").read_bytes() == (wu / f"single{k}.cand").read_bytes()
+        assert not (wu / f"par.cpt.{k}").exists()
+    r = subprocess.run([str(EXE), "-i", str(wu / "wu.binary")] + pairs("bad") + common, capture_output=True, text=True, timeout=60)
+    assert r.returncode == brp_b200.RADPUL_EMISC and "differ" in r.stderr                # erp_boinc_wrapper.cpp:412-416
+
+
 def test_cli_error_paths(wu):
     run_cli(wu, "--max_templates", "2", "--checkpoint_period", "0")
     (wu / "other.binary").write_bytes((wu / "wu.binary").read_bytes())
