@@ -71,6 +71,29 @@ def test_resample_then_spectrum_matches_golden(golden, tag, padding):
     s.close()
 
 
+@pytest.mark.parametrize("log2nu,padding", [(20, 1.0), (20, 3.0), (21, 1.0), (21, 3.0)])
+def test_short_work_units_resample_then_spectrum(oracle, log2nu, padding):
+    """Work-units of 2^20 and 2^21 samples run a 2048-row (3 x 2048 with -P 3) pass 1 on the persistent tensor-copy kernel and a
+    short pass 2 (brp_fft_plan_create): resample on the device, then the spectrum with the padding applied on load, against the
+    oracle's transform of the materialised padded series."""
+    nu = 1 << log2nu
+    series, _ = synth.make_series(nu, seed=log2nu)
+    g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, padding, 400.0, 1000)
+    s = brp_b200.Search(g, max_batch=1)
+    s.set_series(series)
+    t = brp_b200.derive_template(1462.994097917309, 0.192481315985, 1.753485476554, g.step_inv)
+    out, _, n_steps, mean = s.stage_resample(t, want_series=True, want_index=False)
+    got = s.stage_spectrum()
+    padded = out.copy()
+    padded[n_steps:] = np.float32(mean)
+    want = oracle.power_spectrum(padded, g.nsamples)
+    err, _ = power_close(got, want, RTOL)
+    assert err <= RTOL, err
+    rel = np.linalg.norm(got.astype(np.float64) - want) / np.linalg.norm(want)
+    assert rel < 2e-6, rel
+    s.close()
+
+
 @pytest.mark.parametrize("n", [1 << 22, 3 << 22, 1 << 23])
 def test_full_size_properties(n):
     padding = 3.0 if n % 3 == 0 else 1.0
