@@ -125,7 +125,8 @@ def test_cli_several_work_units_in_one_invocation(wu):
         other[1168:] = np.clip(samples, -128, 127).astype(np.int8).view(np.uint8)
         names.append(f"wu{k}.binary")
         (wu / names[-1]).write_bytes(other.tobytes())
-    common = ["-t", str(wu / "bank.txt"), "-f", "400", "-A", "0.08", "-P", "1.0", "-B", "200", "-z"]
+    (wu / "zap.txt").write_text("50.0 50.5\n")       # whitening with a zap range too: concurrent passes each whiten their own series
+    common = ["-t", str(wu / "bank.txt"), "-f", "400", "-A", "0.08", "-P", "1.0", "-B", "200", "-z", "-W", "-l", str(wu / "zap.txt")]
     for k, name in enumerate(names):                # one invocation each: the expected files
         r = subprocess.run([str(EXE), "-i", str(wu / name), "-o", str(wu / f"single{k}.cand")] + common, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
