@@ -84,6 +84,24 @@ def test_search_matches_oracle(oracle, log2nu, padding, n_templates, max_batch):
     assert min(abs(f_best * h - 173.7) for h in (1, 2, 4, 8, 16)) < 0.5
 
 
+@pytest.mark.parametrize("nu,n,n_templates", [(50000, 1 << 16, 12), (3000000, 1 << 22, 4), (1400000, 3 << 20, 4)])
+def test_search_with_ragged_unpadded_length(oracle, nu, n, n_templates):
+    """The reference pads any Nu to N = (int)(padding * Nu + 0.5) (demod_binary.c:782); here N must be 2^a or 3 * 2^a but Nu is
+    free.  A Nu that does not fill whole tensor-copy boxes makes FFT pass 1 take the plain kernel (pass1_tma_maps): same toplist."""
+    padding = n / nu
+    puls = synth.Pulsar(P_orb=30.0, tau=0.01, Psi0=2.5, summed_power=160.0)
+    series, _ = synth.make_series(nu, seed=nu % 1000, pulsar=puls)
+    bank = small_bank(n_templates, seed=7)
+    bank[1] = (puls.P_orb, puls.tau, puls.Psi0)
+    g = brp_b200.derive_geometry(nu, synth.TSAMPLE_US, padding, 400.0, 200)
+    go = oracle.geometry(nu, synth.TSAMPLE_US, padding, 400.0, 200)
+    assert g.nsamples == n and go.nsamples == n
+    cands, tidx = brp_b200.search_bank(series, g, bank, fA=0.08, max_batch=3)
+    want, want_t = oracle.search(series, go, 0.08, bank)
+    _compare_toplists(cands, tidx, want, want_t)
+    assert np.count_nonzero(want["power"]) >= 5
+
+
 def test_sharded_search_merges_to_the_same_toplist(oracle):
     """contiguous template shards searched independently, hit lists concatenated on the host."""
     nu = 1 << 16
