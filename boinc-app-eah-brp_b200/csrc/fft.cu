@@ -258,8 +258,9 @@ struct GroupSync {
     __device__ __forceinline__ void sync() const { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(NT) : "memory"); }
 };
 
-template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, bool TREE = false, typename Load, typename Store,
-          typename Sync = CtaSync>
+// TW_SMEM: `tw` points into shared memory (a copy of the table made by the kernel), read with plain loads
+template <int L, int ROWS, int STAGE, int MAP, bool ROT, bool SYNC_AFTER_LOAD = false, bool TREE = false, bool TW_SMEM = false, typename Load,
+          typename Store, typename Sync = CtaSync>
 __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const Load &load, const Store &store, const Sync &sy = Sync())
 {
     constexpr int R = cfg_radix(L, STAGE);
@@ -302,7 +303,7 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
             // (measured: 0.17 L1 wavefronts per element in pass 1).  Load W_n^p once and square/multiply up to
             // W_n^{p q}: the product tree is at most log2(R) deep, i.e. a few ulp.
             float2 w[R];
-            w[1] = __ldg(twp);
+            w[1] = TW_SMEM ? *twp : __ldg(twp);
 #pragma unroll
             for (int q = 2; q < R; ++q) {
                 int hb = 1;
@@ -319,7 +320,7 @@ __device__ __forceinline__ void tile_stage(const float2 *__restrict__ tw, const 
 #pragma unroll
             for (int q = 0; q < R; ++q) {
                 float2 o = v[out_slot<R>(q)];
-                if (!LAST && q > 0) o = cmul(o, __ldg(twp + (q - 1) * S));
+                if (!LAST && q > 0) o = cmul(o, TW_SMEM ? twp[(q - 1) * S] : __ldg(twp + (q - 1) * S));
                 store.put(sc, q * S, q, o);
             }
         }
@@ -339,14 +340,14 @@ struct SmemIO {
 };
 
 // middle stages (shared -> shared), recursively unrolled over the stage index
-template <int L, int ROWS, int PASS, int STAGE, int END, typename Sync = CtaSync>
+template <int L, int ROWS, int PASS, int STAGE, int END, typename Sync = CtaSync, bool TW_SMEM = false>
 __device__ __forceinline__ void tile_middle(const float2 *tw, float2 *sm, const Sync &sy = Sync())
 {
     if constexpr (STAGE < END) {
         SmemIO<L, ROWS, PASS> io{sm};
-        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false>(tw, io, io, sy); // (a power tree here is slower: measured 257 vs 250 us)
+        tile_stage<L, ROWS, STAGE, MAP_BF_FAST, false, false, false, TW_SMEM>(tw, io, io, sy); // (a power tree here is slower: measured 257 vs 250 us)
         sy.sync();
-        tile_middle<L, ROWS, PASS, STAGE + 1, END>(tw, sm, sy);
+        tile_middle<L, ROWS, PASS, STAGE + 1, END, Sync, TW_SMEM>(tw, sm, sy);
     }
 }
 
@@ -647,6 +648,12 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
 #ifndef BRP_FFT_P1_PERSIST
 #define BRP_FFT_P1_PERSIST 1
 #endif
+#ifndef BRP_FFT_P1_TB_SMEM
+#define BRP_FFT_P1_TB_SMEM 1 // 0: the last stage of the persistent pass 1 reads tb[col][q] from global memory (A/B runs)
+#endif
+#ifndef BRP_FFT_P1_TW_SMEM
+#define BRP_FFT_P1_TW_SMEM 1 // 0: the persistent pass 1 reads its in-tile twiddles from global memory in every tile (A/B runs)
+#endif
 #ifndef BRP_FFT_P1_BOXWISE
 #define BRP_FFT_P1_BOXWISE 1 // 0: reload a buffer only after ALL stores of the tile have read it (A/B runs)
 #endif
@@ -663,6 +670,9 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
     static_assert(BUF % 128 == 0, "tile buffers must keep the 128-byte alignment of tensor copies");
     extern __shared__ __align__(128) unsigned char smraw[];
     __shared__ __align__(8) unsigned long long full[3];
+    // second factors of the inter-pass twiddle for the tile's four columns (tb[col][0..RL)): 256 contiguous bytes per tile, fetched by a
+    // bulk copy together with the tile instead of seven global loads per thread in the last stage
+    __shared__ __align__(128) float2 tbs[3][BRP_FFT_P1_TB_SMEM ? ROWS * RL : 1];
     const int half = threadIdx.x >> 9, t = threadIdx.x & 511;
     const GroupSync<512> sy{1 + half, t};
     // tiles of this CTA: g(n) = blockIdx.x + n * gridDim.x  ->  (column tile bx, part, template b), bx fastest
@@ -683,13 +693,31 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
         const uint32_t boxes = (rows_needed + kTmaBox - 1) / kTmaBox;
         const uint32_t bar_a = smem_addr(&full[n % 3]);
         float2 *dst = reinterpret_cast<float2 *>(smraw + (size_t)(n % 3) * BUF);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(boxes * kTmaBox * ROWS * 8u) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a),
+                     "r"(boxes * kTmaBox * ROWS * 8u + (BRP_FFT_P1_TB_SMEM ? ROWS * RL * 8u : 0u))
+                     : "memory");
+        if (BRP_FFT_P1_TB_SMEM)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(&tbs[n % 3][0])),
+                         "l"(tb + (size_t)bx * ROWS * RL), "r"(ROWS * RL * 8), "r"(bar_a)
+                         : "memory");
         for (uint32_t k = 0; k < boxes; ++k)
             asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
                              smem_addr(dst + k * kTmaBox * ROWS)),
                          "l"(&in_map), "r"((int)(2u * bx * ROWS)), "r"((int)(k * kTmaBox)), "r"((int)b), "r"(bar_a)
                          : "memory");
     };
+    // The in-tile twiddles the kernel reads are thread constants: W^p of stage 0's product tree (128 values) and the table of
+    // stage 1 (15 x 8).  Fetched from global memory in every tile they miss the few KB of L1 the three tile buffers leave, and the first
+    // of them -- behind the wait for the tile, at the head of the dependency chain -- was the largest single stall of the kernel (10 %
+    // of the warp samples on that one load).  A 2 KB copy in shared memory serves them instead.
+    static_assert(NS == 3 && ROWS * (L / cfg_radix(L, 0)) == 512 && !Layout<L, ROWS, 3>::ROT0, "stage 0: one butterfly per thread, plain row-fast lanes");
+    constexpr int TW0 = cfg_stride(L, 0), TW1 = (cfg_radix(L, 1) - 1) * cfg_stride(L, 1);
+    __shared__ float2 tws[BRP_FFT_P1_TW_SMEM ? TW0 + TW1 : 1];
+    if (BRP_FFT_P1_TW_SMEM && threadIdx.x < TW0 + TW1)
+        tws[threadIdx.x] = __ldg(tw + (threadIdx.x < TW0 ? cfg_tw_offset(L, 0) + (int)threadIdx.x : cfg_tw_offset(L, 1) + (int)threadIdx.x - TW0));
+    // pointers such that the stages' own offsets (cfg_tw_offset + ...) land in the copy
+    const float2 *const tw_s0 = BRP_FFT_P1_TW_SMEM ? tws - cfg_tw_offset(L, 0) : tw;
+    const float2 *const tw_s1 = BRP_FFT_P1_TW_SMEM ? tws + TW0 - cfg_tw_offset(L, 1) : tw;
     if (threadIdx.x == 0) {
         for (int k = 0; k < 3; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&full[k])));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -716,9 +744,9 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
         }
         SmemIO<L, ROWS, 3> io{sm};
         const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, part, PARTS, part > 0 ? tw_parts + (part - 1) * kTmaL : tw_parts};
-        tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true>(tw, dload, io, sy);
+        tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true, false, BRP_FFT_P1_TW_SMEM != 0>(tw_s0, dload, io, sy);
         sy.sync();
-        tile_middle<L, ROWS, 3, 1, NS - 1>(tw, sm, sy);
+        tile_middle<L, ROWS, 3, 1, NS - 1, GroupSync<512>, BRP_FFT_P1_TW_SMEM != 0>(tw_s1, sm, sy);
 
         constexpr int PER = ROWS * (L / RL) / 512;
         float2 v[PER][RL];
@@ -746,11 +774,11 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
             const uint32_t k2b = PARTS > 1 ? (uint32_t)PARTS * (uint32_t)kb_[it] + (uint32_t)part : (uint32_t)kb_[it];
             sincospif(-2.0f * (float)(col * k2b) * inv_m, &sn, &cs);
             const float2 a = make_float2(cs, sn);
-            const float2 *__restrict__ tq = tb + (size_t)col * RL;
+            const float2 *__restrict__ tq = BRP_FFT_P1_TB_SMEM ? &tbs[n % 3][rows_[it] * RL] : tb + (size_t)col * RL;
             float2 *d = sm + kb_[it] * ROWS + rows_[it];
 #pragma unroll
             for (int q = 0; q < RL; ++q) {
-                const float2 w = (q == 0) ? a : cmul(a, __ldg(tq + q));
+                const float2 w = (q == 0) ? a : cmul(a, BRP_FFT_P1_TB_SMEM ? tq[q] : __ldg(tq + q));
                 d[q * (L / RL) * ROWS] = cmul(v[it][out_slot<RL>(q)], w);
             }
         }
@@ -780,8 +808,14 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
                 decode(n + 3, bx3, part3, b3);
                 const uint32_t need3 = min((uint32_t)L, (n_steps_arr[b3] + 2u * m1 - 1u) / (2u * m1));
                 boxes3 = (need3 + kTmaBox - 1) / kTmaBox;
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&full[n % 3])), "r"(boxes3 * kTmaBox * ROWS * 8u)
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&full[n % 3])),
+                             "r"(boxes3 * kTmaBox * ROWS * 8u + (BRP_FFT_P1_TB_SMEM ? ROWS * RL * 8u : 0u))
                              : "memory");
+                if (BRP_FFT_P1_TB_SMEM) // everybody of this half is past its reads of the slot (the barrier above)
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                     smem_addr(&tbs[n % 3][0])),
+                                 "l"(tb + (size_t)bx3 * ROWS * RL), "r"(ROWS * RL * 8), "r"(smem_addr(&full[n % 3]))
+                                 : "memory");
             }
             static_assert(L / kTmaBox == 8, "eight boxes per tile");
 #define BRP_RELOAD_BOX(k)                                                                                                               \
