@@ -478,6 +478,7 @@ struct TmaDenseLoad {
     float mean;
     int part, parts;
     const float2 *twq; // W_{m2}^{q p}, p < 2048 (part > 0)
+    bool twq_smem = false; // twq is the kernel's shared-memory copy of the row q = 1; q = 2 squares it
     struct Ctx {
         const float2 *p;
         const float2 *t;
@@ -505,6 +506,10 @@ struct TmaDenseLoad {
         const float c2 = mean + mean; // parts = 3: the same operations as Dft<3> on (v, c, c)
         if (part == 0) return parts == 3 ? cadd(v, make_float2(c2, c2)) : cadd(v, make_float2(mean, mean));
         const float2 d = parts == 3 ? make_float2(fmaf(-0.5f, c2, v.x), fmaf(-0.5f, c2, v.y)) : make_float2(v.x - mean, v.y - mean);
+        if (twq_smem) {
+            const float2 w = c.t[off];
+            return cmul(d, part == 2 ? cmul(w, w) : w);
+        }
         return cmul(d, __ldg(c.t + off));
     }
 };
@@ -648,6 +653,9 @@ fft_pass1_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
 #ifndef BRP_FFT_P1_PERSIST
 #define BRP_FFT_P1_PERSIST 1
 #endif
+#ifndef BRP_FFT_P1_TWQ_SMEM
+#define BRP_FFT_P1_TWQ_SMEM 1 // 0: the persistent pass 1 with PARTS > 1 reads W^{qp} from global memory (A/B runs)
+#endif
 #ifndef BRP_FFT_P1_TB_SMEM
 #define BRP_FFT_P1_TB_SMEM 1 // 0: the last stage of the persistent pass 1 reads tb[col][q] from global memory (A/B runs)
 #endif
@@ -718,6 +726,12 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
     // pointers such that the stages' own offsets (cfg_tw_offset + ...) land in the copy
     const float2 *const tw_s0 = BRP_FFT_P1_TW_SMEM ? tws - cfg_tw_offset(L, 0) : tw;
     const float2 *const tw_s1 = BRP_FFT_P1_TW_SMEM ? tws + TW0 - cfg_tw_offset(L, 1) : tw;
+    // PARTS > 1: the twiddles W^{qp} of the folded first stage (sixteen per thread and tile) come from a shared-memory copy of the row
+    // q = 1 as well (16 KB, all that is left beside the three buffers); the row q = 2 is its square
+    constexpr bool TWQ = BRP_FFT_P1_TWQ_SMEM != 0 && PARTS > 1;
+    __shared__ float2 twq1[TWQ ? L : 1];
+    if (TWQ)
+        for (int i = threadIdx.x; i < L; i += 1024) twq1[i] = __ldg(tw_parts + i);
     if (threadIdx.x == 0) {
         for (int k = 0; k < 3; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&full[k])));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -743,7 +757,7 @@ fft_pass1_persist_kernel(const __grid_constant__ CUtensorMap in_map, const __gri
                              : "memory");
         }
         SmemIO<L, ROWS, 3> io{sm};
-        const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, part, PARTS, part > 0 ? tw_parts + (part - 1) * kTmaL : tw_parts};
+        const TmaDenseLoad dload{sm, m1, col0, n_steps, mean, part, PARTS, TWQ ? twq1 : (part > 0 ? tw_parts + (part - 1) * kTmaL : tw_parts), TWQ};
         tile_stage<L, ROWS, 0, MAP_ROW_FAST, Layout<L, ROWS, 3>::ROT0, true, false, BRP_FFT_P1_TW_SMEM != 0>(tw_s0, dload, io, sy);
         sy.sync();
         tile_middle<L, ROWS, 3, 1, NS - 1, GroupSync<512>, BRP_FFT_P1_TW_SMEM != 0>(tw_s1, sm, sy);
