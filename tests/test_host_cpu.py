@@ -43,6 +43,43 @@ def test_no_cpu_fallback_without_gpu():
         brp_b200.stage_sin_lut(np.zeros(4, np.float32))
 
 
+def test_command_line_driver_argument_handling_and_no_cpu_fallback(tmp_path):
+    """brp_b200_search: option checks of demod_binary.c:221-439 and of the wrapper's -i/-o pairing (erp_boinc_wrapper.cpp:412-416)
+    happen before any device is touched; with a valid work-unit and no GPU the program must fail with the library's code."""
+    import subprocess
+    exe = Path(__file__).resolve().parent.parent / "boinc-app-eah-brp_b200" / "brp_b200_search"
+    assert exe.exists(), "brp_b200_search not built (python boinc-app-eah-brp_b200/build.py)"
+
+    def run(*args):
+        return subprocess.run([str(exe)] + [str(a) for a in args], capture_output=True, text=True, timeout=120)
+
+    assert run("-P", "0.5").returncode == brp_b200.RADPUL_EVAL
+    assert run("-f", "-1").returncode == brp_b200.RADPUL_EVAL
+    assert run("-A", "2").returncode == brp_b200.RADPUL_EVAL
+    assert run("-B", "300000").returncode == brp_b200.RADPUL_EVAL
+    assert run("--devices", "1-0").returncode == brp_b200.RADPUL_EVAL
+    assert run("-i", "x.dat", "-o", "o", "-t", "t").returncode == brp_b200.RADPUL_EFILE     # extension, demod_binary.c:318
+    assert run("-o", "o", "-t", "t").returncode == brp_b200.RADPUL_EMISC                     # no input
+    assert run("-q").returncode == brp_b200.RADPUL_EMISC and run("-i").returncode == brp_b200.RADPUL_EMISC
+    r = run("-i", "a.binary", "-i", "b.binary", "-o", "x", "-t", "t")
+    assert r.returncode == brp_b200.RADPUL_EMISC and "differ" in r.stderr
+    r = run("-i", tmp_path / "missing.binary", "-o", tmp_path / "o", "-t", tmp_path / "t")
+    assert r.returncode == brp_b200.RADPUL_EIO                                                # demod_binary.c:657-661
+    try:
+        import torch
+        if torch.cuda.is_available():
+            return
+    except ImportError:
+        pass
+    _, q = golden_case_C()
+    synth.write_binary_wu(tmp_path / "wu.binary", q)
+    synth.write_bank(tmp_path / "bank.txt", synth.make_bank(4))
+    r = run("-i", tmp_path / "wu.binary", "-o", tmp_path / "out.cand", "-t", tmp_path / "bank.txt", "-f", "400", "-B", "200")
+    # (a process exit status keeps the low eight bits of the RADPUL code; the code itself is in the message)
+    assert r.returncode == brp_b200.RADPUL_CUDA_DEVICE_FIND % 256 and f"code {brp_b200.RADPUL_CUDA_DEVICE_FIND}" in r.stderr, r.stderr
+    assert "no CPU fallback" in r.stderr and not (tmp_path / "out.cand").exists()
+
+
 @pytest.mark.parametrize("nu,pad,f0,win", [(1 << 22, 1.0, 400.0, 1000), (1 << 22, 3.0, 400.0, 1000), (1 << 22, 2.0, 400.0, 1000),
                                            (1 << 20, 1.0, 400.0, 1000), (1 << 14, 1.0, 400.0, 200), (1 << 16, 3.0, 250.0, 1000),
                                            (1 << 15, 1.0, 5000.0, 100)])
